@@ -1,0 +1,131 @@
+/*
+ * sr_cuda.h — C ABI of libsr_cuda.so, the B200 (sm_100a) implementation of the CPU rasterization path of
+ * zhvrnkov/software-renderer.
+ *
+ * What it replaces ("R:" = renderer/Renderer.swift, "G:" = renderer/GpuRenderer.swift, "A:" = renderer/App.swift
+ * in the reference tree):
+ *   the seam is `func render(renderPass: RenderPass)` — Renderer R:204-230 (CPU) / GpuRenderer G:35-90 (Metal),
+ *   called once per frame from A:185.  A Swift `CudaRenderer.render(renderPass:)` (swift/ in this repo) binds the
+ *   functions below through a module map; data layouts are the reference's own, so the Swift
+ *   arrays are passed without conversion:
+ *     vertices : Swift `Vertex` R:154-157 = 2 x SIMD3<Float> = 32 bytes (x y z pad r g b pad)
+ *     indices  : Swift `[Int]`  R:196     = int64
+ *     transform: matrix_float4x4 R:199    = 16 floats, column-major
+ *     colour   : `Pixel` R:44-49          = 4 bytes b,g,r,a; packed rows, y*width+x (A:351-360)
+ *     depth    : Float per pixel (DepthImage R:6)
+ *
+ * Semantics are Renderer.swift's, bit for bit: clear to (0,0,0,0)/+inf (R:205-206), integer
+ * scan-line coverage (R:271-283, R:467-494), "highest primitive index wins" visibility (the depth test is
+ * commented out at R:257-261), barycentric colour (R:263-268).  SR_FLAG_DEPTH_LESS enables the commented-out
+ * depth test as written there (strict <, so the earliest index wins ties).
+ *
+ * Error behaviour: the reference traps (R:226 index out of range, R:251/R:271/R:298 Int(Float) of NaN/inf/huge,
+ * R:492 overflow).  This library never aborts: functions return 0 or a negative sr_status.  A primitive with a
+ * corner whose screen x or y is not finite or has |.| >= 2^30 is skipped and counted; the frame is completed and
+ * the call returns SR_ERR_DOMAIN.
+ *
+ * Threading: one sr_ctx per GPU; a context is single-threaded, like the reference renderer.
+ * There is no CPU fallback: without a CUDA device sr_create fails with SR_ERR_CUDA.
+ */
+#ifndef SR_CUDA_H
+#define SR_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sr_ctx sr_ctx;
+
+/* PrimitiveType, R:174-189 (verticesCount: triangle 3, line 2, vertices 3) */
+typedef enum sr_primitive { SR_TRIANGLE = 0, SR_LINE = 1, SR_VERTICES = 2 } sr_primitive;
+
+typedef enum sr_status {
+    SR_OK = 0,
+    SR_ERR_ARG = -1,     /* null pointer, non-positive size, unknown primitive type */
+    SR_ERR_INDEX = -2,   /* an index is negative or >= nverts (reference: array trap, R:226) */
+    SR_ERR_DOMAIN = -3,  /* >=1 primitive skipped: corner outside the valid domain (reference: trap, R:251) */
+    SR_ERR_CUDA = -4,    /* CUDA runtime failure, or no device; see sr_last_error */
+    SR_ERR_NOMESH = -5   /* render called before sr_set_mesh */
+} sr_status;
+
+enum {
+    SR_FLAG_DEPTH_LESS = 1u << 0, /* run the depth test of R:257-261 (off = reference as shipped) */
+    SR_FLAG_NO_DEPTH_OUT = 1u << 1 /* do not produce / copy back the depth image (depth pointer may be NULL) */
+};
+
+/* Same bytes as Swift's Vertex (R:154-157). */
+typedef struct sr_vertex {
+    float x, y, z, _pad0;
+    float r, g, b, _pad1;
+} sr_vertex;
+
+/* Per-context counters of the most recent render call (all views of a batch summed). */
+typedef struct sr_stats {
+    uint64_t primitives;      /* primitives submitted */
+    uint64_t domain_skipped;  /* primitives (SR_VERTICES: corners) skipped by the domain rule */
+    uint64_t small_tris;      /* triangles rasterized by the direct (per-triangle) path */
+    uint64_t binned_tris;     /* triangles sent through tile binning */
+    uint64_t tile_pairs;      /* (triangle, tile) pairs produced by binning */
+    uint64_t bin_regrows;     /* times a frame was re-run because the pair buffer had to grow */
+    uint64_t gpu_launches;    /* kernels launched by the call */
+    float    gpu_ms;          /* device time of the call's kernels, CUDA events on the context's stream */
+} sr_stats;
+
+/* -- lifetime -------------------------------------------------------------------------------------------------- */
+/* Replaces `Renderer()` / `GpuRenderer()` construction (A:148-149).  `device` is a CUDA ordinal. */
+int sr_create(sr_ctx** out, int device);
+void sr_destroy(sr_ctx* ctx);
+const char* sr_last_error(const sr_ctx* ctx);
+/* library / ABI version: major*1000 + minor */
+int sr_version(void);
+
+/* -- mesh -------------------------------------------------------------------------------------------------------
+ * RenderPass.vertices / RenderPass.indices (R:195-196).  The reference hands both arrays over on every frame
+ * (A:163); GpuRenderer caches its device buffers across frames (G:41-67).  Here the upload is explicit: call again
+ * whenever the arrays change.  A trailing partial primitive is ignored, as R:221 does. */
+int sr_set_mesh(sr_ctx* ctx, const sr_vertex* vertices, size_t nverts, const int64_t* indices, size_t nidx);
+
+/* -- render ---------------------------------------------------------------------------------------------------- */
+/* render(renderPass:) R:204-230 on the uploaded mesh: synchronous, writes host memory the caller owns
+ * (A:80-101).  `color_bgra` = width*height*4 bytes, `depth` = width*height floats (may be NULL with
+ * SR_FLAG_NO_DEPTH_OUT). */
+int sr_render(sr_ctx* ctx, const float* transform_colmajor16, int primitive_type, int width, int height,
+              uint8_t* color_bgra, float* depth, uint32_t flags);
+
+/* One call = RenderPass as the reference passes it (vertices and indices travel with the call, A:163):
+ * sr_set_mesh + sr_render. */
+int sr_render_pass(sr_ctx* ctx, const sr_vertex* vertices, size_t nverts, const int64_t* indices, size_t nidx,
+                   const float* transform_colmajor16, int primitive_type, int width, int height,
+                   uint8_t* color_bgra, float* depth, uint32_t flags);
+
+/* `nviews` independent render passes of the same mesh (one matrix each; the reference renders them one call at a
+ * time).  Outputs are nviews consecutive images in host memory. */
+int sr_render_batch(sr_ctx* ctx, const float* transforms_colmajor16, size_t nviews, int primitive_type,
+                    int width, int height, uint8_t* color_bgra, float* depth, uint32_t flags);
+
+/* Device-resident variant: outputs are DEVICE pointers (nviews consecutive images), work is enqueued on
+ * `cuda_stream` (a cudaStream_t, NULL = the context's own stream) and the call returns without waiting.
+ * `transforms_colmajor16` is host memory and is copied before return.  Follow with sr_sync. */
+int sr_render_device(sr_ctx* ctx, const float* transforms_colmajor16, size_t nviews, int primitive_type,
+                     int width, int height, void* color_bgra_dev, void* depth_dev, uint32_t flags,
+                     void* cuda_stream);
+
+/* Waits for the work enqueued by sr_render_device and returns its status (SR_OK / SR_ERR_DOMAIN / SR_ERR_CUDA). */
+int sr_sync(sr_ctx* ctx);
+
+/* Counters of the last completed render call. */
+int sr_get_stats(sr_ctx* ctx, sr_stats* out);
+
+/* Per-kernel device times (ms) of the last single-view render, for bench.py's roofline line.
+ * names: up to `cap` pointers to static strings; ms: same length.  Returns the number of entries. */
+int sr_get_kernel_times(sr_ctx* ctx, const char** names, float* ms, int cap);
+/* Enables per-kernel CUDA-event timing (adds events between kernels; off by default). */
+int sr_set_profiling(sr_ctx* ctx, int enabled);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
