@@ -1,0 +1,542 @@
+// sr_api.cu — host side of libsr_cuda.so: context, buffers, launch sequence, C ABI (include/sr_cuda.h).
+// There is no CPU fallback anywhere in this file: without a CUDA device sr_create fails.
+#include "../../include/sr_cuda.h"
+#include "sr_kernels.cuh"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace sr;
+
+namespace {
+
+constexpr int MAX_PROF = 16;
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;   // elements
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void**)&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct sr_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    std::string err;
+
+    // mesh (device format: packed xyz, float4 rgb, int32 indices)
+    DevBuf<float> pos;
+    DevBuf<float4> col;
+    DevBuf<int> idx;
+    size_t nverts = 0, nidx = 0;
+    unsigned long long first_bad = ~0ull;   // position of the first out-of-range index
+    bool has_mesh = false;
+
+    // per-frame working set
+    DevBuf<float4> sv;                      // screen-space vertices (sx, sy, z, 0)
+    DevBuf<TriRec> recs;                    // bin list
+    DevBuf<unsigned> counts, cursor;        // (tile, chunk) counters / list cursors
+    DevBuf<unsigned> pairs;                 // tile lists
+    DevBuf<unsigned> vis32;                 // depth-off visibility words (prim+1), self-clearing
+    DevBuf<unsigned long long> vis64;       // depth-less keys, self-clearing to SR_KEY_EMPTY
+    DevBuf<unsigned long long> look;        // scan look-back array
+    DevBuf<unsigned> ticket;
+    unsigned ticket_base = 0, epoch = 0;
+    DevBuf<ViewStatus> status;
+    ViewStatus* h_status = nullptr;
+    size_t h_status_cap = 0;
+
+    // staging for the host-pointer API (double buffered)
+    DevBuf<uint8_t> out_color[2];
+    DevBuf<float> out_depth[2];
+    cudaEvent_t ev_render[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+
+    // profiling
+    bool profiling = false;
+    cudaEvent_t prof_ev[MAX_PROF + 1] = {};
+    const char* prof_name[MAX_PROF] = {};
+    int prof_n = 0;
+    float prof_ms[MAX_PROF] = {};
+
+    // pending asynchronous call (sr_render_device .. sr_sync)
+    struct Pending {
+        bool active = false;
+        std::vector<float> transforms;
+        size_t nviews = 0;
+        int prim = 0, width = 0, height = 0;
+        uint8_t* color = nullptr;
+        float* depth = nullptr;
+        uint32_t flags = 0;
+        cudaStream_t stream = nullptr;
+    } pending;
+
+    sr_stats stats = {};
+    uint64_t launches = 0;
+};
+
+namespace {
+
+#define SR_CUDA(ctx, expr)                                                                             \
+    do {                                                                                               \
+        cudaError_t e__ = (expr);                                                                      \
+        if (e__ != cudaSuccess) {                                                                      \
+            char b__[512];                                                                             \
+            snprintf(b__, sizeof b__, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            (ctx)->err = b__;                                                                          \
+            return SR_ERR_CUDA;                                                                        \
+        }                                                                                              \
+    } while (0)
+
+int fail(sr_ctx* c, int code, const char* msg) {
+    if (c) c->err = msg;
+    return code;
+}
+
+inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+void prof_mark(sr_ctx* c, cudaStream_t st, const char* name_of_next) {
+    if (!c->profiling || c->prof_n >= MAX_PROF) return;
+    cudaEventRecord(c->prof_ev[c->prof_n], st);
+    c->prof_name[c->prof_n] = name_of_next;
+    c->prof_n++;
+}
+
+int primitive_vertices(int prim) { return prim == SR_LINE ? 2 : 3; }   // R:179-188
+
+// Make sure the per-frame buffers fit this mesh and resolution.  Newly allocated self-clearing buffers are put
+// into their cleared state here; afterwards the kernels keep them clean.
+int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews, cudaStream_t st) {
+    const size_t npx = (size_t)W * H;
+    const size_t tiles = (size_t)div_up(W, TILE) * div_up(H, TILE);
+    const size_t ncnt = tiles * NCHUNK;
+    const size_t ntris = c->nidx / 3;
+    SR_CUDA(c, c->sv.reserve(std::max<size_t>(c->nverts, 1)));
+    SR_CUDA(c, c->recs.reserve(std::max<size_t>(ntris, 1)));
+    if (ncnt > c->counts.cap) {
+        SR_CUDA(c, c->counts.reserve(ncnt));
+        SR_CUDA(c, cudaMemsetAsync(c->counts.p, 0, ncnt * sizeof(unsigned), st));
+    }
+    SR_CUDA(c, c->cursor.reserve(ncnt));
+    const size_t nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
+    if (nblocks > c->look.cap) {
+        SR_CUDA(c, c->look.reserve(nblocks));
+        SR_CUDA(c, cudaMemsetAsync(c->look.p, 0, nblocks * sizeof(unsigned long long), st));
+        c->epoch = 0;
+    }
+    if (!c->ticket.p) {
+        SR_CUDA(c, c->ticket.reserve(1));
+        SR_CUDA(c, cudaMemsetAsync(c->ticket.p, 0, sizeof(unsigned), st));
+        c->ticket_base = 0;
+    }
+    if (!c->pairs.p) {
+        size_t want = std::min<size_t>(std::max<size_t>(4 * ntris, 1u << 20), 64u << 20);
+        SR_CUDA(c, c->pairs.reserve(want));
+    }
+    if (depth_mode) {
+        if (npx > c->vis64.cap) {
+            SR_CUDA(c, c->vis64.reserve(npx));
+            k_fill_u64<<<div_up(npx, 256), 256, 0, st>>>(c->vis64.p, npx, SR_KEY_EMPTY);
+            SR_CUDA(c, cudaGetLastError());
+        }
+    }
+    if (npx > c->vis32.cap) {   // also used by .vertices in either mode
+        SR_CUDA(c, c->vis32.reserve(npx));
+        SR_CUDA(c, cudaMemsetAsync(c->vis32.p, 0, npx * sizeof(unsigned), st));
+    }
+    SR_CUDA(c, c->status.reserve(nviews));
+    if (nviews > c->h_status_cap) {
+        if (c->h_status) cudaFreeHost(c->h_status);
+        c->h_status = nullptr; c->h_status_cap = 0;
+        SR_CUDA(c, cudaMallocHost((void**)&c->h_status, nviews * sizeof(ViewStatus)));
+        c->h_status_cap = nviews;
+    }
+    return SR_OK;
+}
+
+// Enqueue one render pass (R:204-230) on `st`.  Outputs are device pointers.
+int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint8_t* color_dev, float* depth_dev,
+                 uint32_t flags, cudaStream_t st, ViewStatus* d_status) {
+    const bool depth_mode = (flags & SR_FLAG_DEPTH_LESS) != 0 && prim == SR_TRIANGLE;
+    if (flags & SR_FLAG_NO_DEPTH_OUT) depth_dev = nullptr;
+    const size_t npx = (size_t)W * H;
+    Mat4 M;
+    std::memcpy(M.m, transform, sizeof M.m);
+    const int nverts = (int)c->nverts;
+    unsigned* color32 = reinterpret_cast<unsigned*>(color_dev);
+    c->prof_n = 0;
+
+    if (prim != SR_LINE && nverts > 0) {
+        prof_mark(c, st, "k_transform");
+        k_transform<<<div_up(nverts, 256), 256, 0, st>>>(c->pos.p, nverts, M, (float)W, (float)H, c->sv.p);
+        c->launches++;
+    }
+    if (prim == SR_TRIANGLE) {
+        FrameParams fp;
+        fp.width = W; fp.height = H;
+        fp.tiles_x = (int)div_up(W, TILE); fp.tiles_y = (int)div_up(H, TILE);
+        fp.ntris = (int)(c->nidx / 3);
+        fp.chunk_shift = 0;
+        while (fp.ntris > 0 && ((fp.ntris - 1) >> fp.chunk_shift) >= NCHUNK) fp.chunk_shift++;
+        fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
+        const int ntiles = fp.tiles_x * fp.tiles_y;
+        const int ncnt = ntiles * NCHUNK;
+        if (fp.ntris > 0) {
+            prof_mark(c, st, "k_setup");
+            if (depth_mode) k_setup<true><<<div_up(fp.ntris, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, d_status);
+            else            k_setup<false><<<div_up(fp.ntris, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, d_status);
+            c->launches++;
+        }
+        const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
+        c->epoch++;
+        prof_mark(c, st, "k_scan");
+        k_scan<<<nblocks, SCAN_THREADS, 0, st>>>(c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, d_status);
+        c->ticket_base += nblocks;
+        c->launches++;
+        if (fp.ntris > 0) {
+            prof_mark(c, st, "k_bin_fill");
+            const unsigned grid = std::min<unsigned>(div_up(fp.ntris, 256), 148 * 8);
+            k_bin_fill<<<grid, 256, 0, st>>>(c->recs.p, d_status, fp, c->cursor.p, c->pairs.p);
+            c->launches++;
+        }
+        ShadeIn in{c->idx.p, c->sv.p, c->col.p};
+        prof_mark(c, st, "k_tile");
+        if (depth_mode) k_tile<true><<<ntiles, 256, 0, st>>>(fp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, color32, depth_dev);
+        else            k_tile<false><<<ntiles, 256, 0, st>>>(fp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, color32, depth_dev);
+        c->launches++;
+    } else {
+        if (prim == SR_VERTICES) {
+            const int ncorners = (int)((c->nidx / 3) * 3);
+            if (ncorners > 0) {
+                prof_mark(c, st, "k_points_scatter");
+                k_points_scatter<<<div_up(ncorners, 256), 256, 0, st>>>(c->idx.p, c->sv.p, ncorners, W, H, c->vis32.p, d_status);
+                c->launches++;
+            }
+        }
+        prof_mark(c, st, "k_points_resolve");
+        k_points_resolve<<<div_up(npx, 256), 256, 0, st>>>(c->idx.p, c->col.p, npx, c->vis32.p, color32, depth_dev);
+        c->launches++;
+    }
+    prof_mark(c, st, nullptr);
+    SR_CUDA(c, cudaGetLastError());
+    return SR_OK;
+}
+
+int check_args(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, const void* color,
+               const void* depth, uint32_t flags) {
+    if (!c) return SR_ERR_ARG;
+    if (!transforms || !color || nviews == 0) return fail(c, SR_ERR_ARG, "null transform/colour pointer or zero views");
+    if (!depth && !(flags & SR_FLAG_NO_DEPTH_OUT)) return fail(c, SR_ERR_ARG, "depth pointer is null without SR_FLAG_NO_DEPTH_OUT");
+    if (W <= 0 || H <= 0 || (size_t)W * H > (1u << 30)) return fail(c, SR_ERR_ARG, "bad image size");
+    if (prim < SR_TRIANGLE || prim > SR_VERTICES) return fail(c, SR_ERR_ARG, "unknown primitive type");
+    if (!c->has_mesh) return fail(c, SR_ERR_NOMESH, "sr_set_mesh has not been called");
+    const size_t per = primitive_vertices(prim);
+    const size_t used = (c->nidx / per) * per;                 // R:221: trailing partial primitive ignored
+    if (c->first_bad < used) return fail(c, SR_ERR_INDEX, "index out of range (the reference traps at Renderer.swift:226)");
+    return SR_OK;
+}
+
+// Reads the per-view status words back, grows the pair buffer and reports which views must be re-run.
+int collect_status(sr_ctx* c, size_t nviews, cudaStream_t st, std::vector<size_t>* rerun) {
+    SR_CUDA(c, cudaMemcpyAsync(c->h_status, c->status.p, nviews * sizeof(ViewStatus), cudaMemcpyDeviceToHost, st));
+    SR_CUDA(c, cudaStreamSynchronize(st));
+    unsigned need = 0;
+    for (size_t i = 0; i < nviews; ++i) {
+        const ViewStatus& s = c->h_status[i];
+        if (s.total_pairs > c->pairs.cap) { rerun->push_back(i); need = std::max(need, s.total_pairs); }
+    }
+    if (!rerun->empty()) {
+        size_t want = (size_t)need + need / 4 + 1024;
+        if (want > 0xFFFFFFF0ull) return fail(c, SR_ERR_CUDA, "tile lists exceed 2^32 entries");
+        SR_CUDA(c, c->pairs.reserve(want));
+        c->stats.bin_regrows++;
+    }
+    return SR_OK;
+}
+
+void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
+    const size_t per = primitive_vertices(prim);
+    for (size_t i = 0; i < nviews; ++i) {
+        const ViewStatus& s = c->h_status[i];
+        c->stats.primitives += c->nidx / per;
+        c->stats.domain_skipped += s.domain_skipped;
+        c->stats.small_tris += s.n_small;
+        c->stats.binned_tris += s.n_large;
+        c->stats.tile_pairs += s.total_pairs;
+    }
+}
+
+void finish_profile(sr_ctx* c) {
+    if (!c->profiling) return;
+    for (int i = 0; i + 1 < c->prof_n; ++i) cudaEventElapsedTime(&c->prof_ms[i], c->prof_ev[i], c->prof_ev[i + 1]);
+}
+
+// Device-output batch on one stream, including overflow re-runs.  Synchronises.
+int run_device_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, uint8_t* color, float* depth,
+                     uint32_t flags, cudaStream_t st, bool already_enqueued) {
+    const size_t npx = (size_t)W * H;
+    if (!already_enqueued) {
+        int rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
+        if (rc) return rc;
+        SR_CUDA(c, cudaMemsetAsync(c->status.p, 0, nviews * sizeof(ViewStatus), st));
+        SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+        for (size_t i = 0; i < nviews; ++i) {
+            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, color + 4 * npx * i, depth ? depth + npx * i : nullptr, flags, st, c->status.p + i);
+            if (rc) return rc;
+        }
+        SR_CUDA(c, cudaEventRecord(c->ev_end, st));
+    }
+    for (int attempt = 0; attempt < 8; ++attempt) {
+        std::vector<size_t> rerun;
+        int rc = collect_status(c, nviews, st, &rerun);
+        if (rc) return rc;
+        if (rerun.empty()) break;
+        for (size_t i : rerun) {
+            SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
+            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, color + 4 * npx * i, depth ? depth + npx * i : nullptr, flags, st, c->status.p + i);
+            if (rc) return rc;
+        }
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
+    c->stats.gpu_ms = ms;
+    finish_profile(c);
+    accumulate_stats(c, nviews, prim);
+    c->stats.gpu_launches = c->launches;
+    return c->stats.domain_skipped ? SR_ERR_DOMAIN : SR_OK;
+}
+
+}  // namespace
+
+// =================================================================================================================
+// C ABI
+// =================================================================================================================
+extern "C" {
+
+int sr_version(void) { return 1000; }
+
+int sr_create(sr_ctx** out, int device) {
+    if (!out) return SR_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return SR_ERR_CUDA;   // no CPU fallback
+    if (cudaSetDevice(device) != cudaSuccess) return SR_ERR_CUDA;
+    sr_ctx* c = new sr_ctx();
+    c->device = device;
+    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < 2; ++i)
+        ok = cudaEventCreateWithFlags(&c->ev_render[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreate(&c->ev_begin) == cudaSuccess && cudaEventCreate(&c->ev_end) == cudaSuccess;
+    for (int i = 0; ok && i <= MAX_PROF; ++i) ok = cudaEventCreate(&c->prof_ev[i]) == cudaSuccess;
+    if (!ok) { sr_destroy(c); return SR_ERR_CUDA; }
+    *out = c;
+    return SR_OK;
+}
+
+void sr_destroy(sr_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release();
+    c->counts.release(); c->cursor.release(); c->pairs.release(); c->vis32.release(); c->vis64.release();
+    c->look.release(); c->ticket.release(); c->status.release();
+    for (int i = 0; i < 2; ++i) {
+        c->out_color[i].release(); c->out_depth[i].release();
+        if (c->ev_render[i]) cudaEventDestroy(c->ev_render[i]);
+        if (c->ev_copy[i]) cudaEventDestroy(c->ev_copy[i]);
+    }
+    if (c->ev_begin) cudaEventDestroy(c->ev_begin);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    for (int i = 0; i <= MAX_PROF; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
+    if (c->h_status) cudaFreeHost(c->h_status);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    delete c;
+}
+
+const char* sr_last_error(const sr_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64_t* indices, size_t nidx) {
+    if (!c) return SR_ERR_ARG;
+    if ((nverts && !vertices) || (nidx && !indices)) return fail(c, SR_ERR_ARG, "null mesh pointer");
+    if (nverts > 0x7FFFFFF0ull || nidx > 3ull * 0x7FFFFFF0ull) return fail(c, SR_ERR_ARG, "mesh too large for 32-bit device indices");
+    SR_CUDA(c, cudaSetDevice(c->device));
+    SR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->has_mesh = false;
+    SR_CUDA(c, c->pos.reserve(std::max<size_t>(3 * nverts, 1)));
+    SR_CUDA(c, c->col.reserve(std::max<size_t>(nverts, 1)));
+    SR_CUDA(c, c->idx.reserve(std::max<size_t>(nidx, 1)));
+    // stage the Swift-layout arrays, convert on the device
+    void* stage = nullptr;
+    const size_t vbytes = nverts * sizeof(sr_vertex), ibytes = nidx * sizeof(int64_t);
+    unsigned long long* d_bad = nullptr;
+    SR_CUDA(c, cudaMalloc(&stage, std::max<size_t>(std::max(vbytes, ibytes), 16)));
+    cudaError_t e = cudaMalloc((void**)&d_bad, sizeof(unsigned long long));
+    if (e != cudaSuccess) { cudaFree(stage); SR_CUDA(c, e); }
+    int rc = SR_OK;
+    do {
+        c->first_bad = ~0ull;
+        if ((e = cudaMemcpyAsync(d_bad, &c->first_bad, sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
+        if (nverts) {
+            if ((e = cudaMemcpyAsync(stage, vertices, vbytes, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
+            k_convert_vertices<<<div_up(nverts, 256), 256, 0, c->stream>>>((const float4*)stage, nverts, c->pos.p, c->col.p);
+        }
+        if (nidx) {
+            if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) break;   // stage is reused
+            if ((e = cudaMemcpyAsync(stage, indices, ibytes, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
+            k_convert_indices<<<div_up(nidx, 256), 256, 0, c->stream>>>((const long long*)stage, nidx, nverts, c->idx.p, d_bad);
+        }
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(&c->first_bad, d_bad, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) break;
+        e = cudaStreamSynchronize(c->stream);
+    } while (0);
+    cudaFree(stage);
+    cudaFree(d_bad);
+    SR_CUDA(c, e);
+    c->nverts = nverts;
+    c->nidx = nidx;
+    c->has_mesh = true;
+    return rc;
+}
+
+int sr_render_device(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, void* color_dev,
+                     void* depth_dev, uint32_t flags, void* cuda_stream) {
+    int rc = check_args(c, transforms, nviews, prim, W, H, color_dev, depth_dev, flags);
+    if (rc) return rc;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    if (c->pending.active) { rc = sr_sync(c); if (rc == SR_ERR_CUDA) return rc; }
+    c->stats = sr_stats{};
+    c->launches = 0;
+    rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
+    if (rc) return rc;
+    const size_t npx = (size_t)W * H;
+    uint8_t* color = (uint8_t*)color_dev;
+    float* depth = (flags & SR_FLAG_NO_DEPTH_OUT) ? nullptr : (float*)depth_dev;
+    SR_CUDA(c, cudaMemsetAsync(c->status.p, 0, nviews * sizeof(ViewStatus), st));
+    SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+    for (size_t i = 0; i < nviews; ++i) {
+        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, color + 4 * npx * i, depth ? depth + npx * i : nullptr, flags, st, c->status.p + i);
+        if (rc) return rc;
+    }
+    SR_CUDA(c, cudaEventRecord(c->ev_end, st));
+    auto& p = c->pending;
+    p.active = true;
+    p.transforms.assign(transforms, transforms + 16 * nviews);
+    p.nviews = nviews; p.prim = prim; p.width = W; p.height = H;
+    p.color = color; p.depth = depth; p.flags = flags; p.stream = st;
+    return SR_OK;
+}
+
+int sr_sync(sr_ctx* c) {
+    if (!c) return SR_ERR_ARG;
+    if (!c->pending.active) return SR_OK;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    auto& p = c->pending;
+    p.active = false;
+    return run_device_batch(c, p.transforms.data(), p.nviews, p.prim, p.width, p.height, p.color, p.depth, p.flags, p.stream, true);
+}
+
+int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, uint8_t* color,
+                    float* depth, uint32_t flags) {
+    int rc = check_args(c, transforms, nviews, prim, W, H, color, depth, flags);
+    if (rc) return rc;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    if (c->pending.active) { rc = sr_sync(c); if (rc == SR_ERR_CUDA) return rc; }
+    c->stats = sr_stats{};
+    c->launches = 0;
+    cudaStream_t st = c->stream;
+    const bool want_depth = !(flags & SR_FLAG_NO_DEPTH_OUT);
+    const size_t npx = (size_t)W * H;
+    rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
+    if (rc) return rc;
+    for (int b = 0; b < 2; ++b) {
+        SR_CUDA(c, c->out_color[b].reserve(4 * npx));
+        if (want_depth) SR_CUDA(c, c->out_depth[b].reserve(npx));
+    }
+    SR_CUDA(c, cudaMemsetAsync(c->status.p, 0, nviews * sizeof(ViewStatus), st));
+    SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+    // render view i into staging buffer i&1 while the copy stream drains the other one
+    for (size_t i = 0; i < nviews; ++i) {
+        const int b = (int)(i & 1);
+        if (i >= 2) SR_CUDA(c, cudaStreamWaitEvent(st, c->ev_copy[b], 0));
+        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[b].p, want_depth ? c->out_depth[b].p : nullptr, flags, st, c->status.p + i);
+        if (rc) return rc;
+        SR_CUDA(c, cudaEventRecord(c->ev_render[b], st));
+        SR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_render[b], 0));
+        SR_CUDA(c, cudaMemcpyAsync(color + 4 * npx * i, c->out_color[b].p, 4 * npx, cudaMemcpyDeviceToHost, c->copy_stream));
+        if (want_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[b].p, npx * sizeof(float), cudaMemcpyDeviceToHost, c->copy_stream));
+        SR_CUDA(c, cudaEventRecord(c->ev_copy[b], c->copy_stream));
+    }
+    SR_CUDA(c, cudaEventRecord(c->ev_end, st));
+    SR_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    // status + overflow re-runs (rare: only while the tile-list buffer is still growing)
+    for (int attempt = 0; attempt < 8; ++attempt) {
+        std::vector<size_t> rerun;
+        rc = collect_status(c, nviews, st, &rerun);
+        if (rc) return rc;
+        if (rerun.empty()) break;
+        for (size_t i : rerun) {
+            SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
+            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[0].p, want_depth ? c->out_depth[0].p : nullptr, flags, st, c->status.p + i);
+            if (rc) return rc;
+            SR_CUDA(c, cudaMemcpyAsync(color + 4 * npx * i, c->out_color[0].p, 4 * npx, cudaMemcpyDeviceToHost, st));
+            if (want_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[0].p, npx * sizeof(float), cudaMemcpyDeviceToHost, st));
+        }
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
+    c->stats.gpu_ms = ms;
+    finish_profile(c);
+    accumulate_stats(c, nviews, prim);
+    c->stats.gpu_launches = c->launches;
+    return c->stats.domain_skipped ? SR_ERR_DOMAIN : SR_OK;
+}
+
+int sr_render(sr_ctx* c, const float* transform, int prim, int W, int H, uint8_t* color, float* depth, uint32_t flags) {
+    return sr_render_batch(c, transform, 1, prim, W, H, color, depth, flags);
+}
+
+int sr_render_pass(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64_t* indices, size_t nidx,
+                   const float* transform, int prim, int W, int H, uint8_t* color, float* depth, uint32_t flags) {
+    int rc = sr_set_mesh(c, vertices, nverts, indices, nidx);
+    if (rc) return rc;
+    return sr_render(c, transform, prim, W, H, color, depth, flags);
+}
+
+int sr_get_stats(sr_ctx* c, sr_stats* out) {
+    if (!c || !out) return SR_ERR_ARG;
+    *out = c->stats;
+    return SR_OK;
+}
+
+int sr_set_profiling(sr_ctx* c, int enabled) {
+    if (!c) return SR_ERR_ARG;
+    c->profiling = enabled != 0;
+    return SR_OK;
+}
+
+int sr_get_kernel_times(sr_ctx* c, const char** names, float* ms, int cap) {
+    if (!c || !names || !ms) return 0;
+    int n = 0;
+    for (int i = 0; i + 1 < c->prof_n && n < cap; ++i, ++n) { names[n] = c->prof_name[i]; ms[n] = c->prof_ms[i]; }
+    return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,141 @@
+// sr_math.cuh — the arithmetic of Renderer.swift, as device functions.
+//
+// Every float operation that decides a coverage bit, a depth bit or a colour byte is written with the
+// round-to-nearest intrinsics (__fmul_rn, __fadd_rn, __fsub_rn, __fdiv_rn), which nvcc never contracts into FMA,
+// in the reference's operation order.  The translation unit is also built with -fmad=false.
+// "R:" = /root/reference/renderer/Renderer.swift.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sr {
+
+struct Mat4 { float m[16]; };  // column-major, like matrix_float4x4 (R:199)
+
+// Vertex.apply (R:159-163) + convertedToScreen (R:165-172).  Returns (sx, sy, z_ndc).
+// matrix * float4 is column accumulation with separately rounded * and + (the definition shared with oracle/).
+__device__ __forceinline__ float3 transform_to_screen(const Mat4& M, float x, float y, float z, float fw, float fh) {
+    float v[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        float acc = __fmul_rn(M.m[r], x);
+        acc = __fadd_rn(acc, __fmul_rn(M.m[4 + r], y));
+        acc = __fadd_rn(acc, __fmul_rn(M.m[8 + r], z));
+        acc = __fadd_rn(acc, __fmul_rn(M.m[12 + r], 1.0f));
+        v[r] = acc;
+    }
+    float nx = __fdiv_rn(v[0], v[3]);   // R:161: three true divisions, no reciprocal
+    float ny = __fdiv_rn(v[1], v[3]);
+    float nz = __fdiv_rn(v[2], v[3]);
+    float ux = __fadd_rn(__fmul_rn(nx, 0.5f), 0.5f);    // R:166
+    float uy = __fadd_rn(__fmul_rn(ny, -0.5f), 0.5f);
+    return make_float3(__fmul_rn(ux, fw), __fmul_rn(uy, fh), nz);   // R:168 (no rounding of the product)
+}
+
+// valid domain: finite and |s| < 2^30 (NaN fails).  Outside it the reference traps (R:251, R:271, R:298).
+__device__ __forceinline__ bool in_domain(float s) { return fabsf(s) < 1073741824.0f; }
+
+// ---- integer span rule (R:467-494) ----------------------------------------------------------------------------
+// start.x + diff*nt/dy, 64-bit product, division truncating toward zero.  dy != 0.
+__device__ __forceinline__ int lerp_trunc(int sx, int sy, int ex, int ey, int t) {
+    long long diff = (long long)ex - (long long)sx;
+    long long nt = (long long)t - (long long)sy;
+    long long dy = (long long)ey - (long long)sy;
+    long long num = diff * nt;
+    long long q;
+    if (num == (long long)(int)num && dy == (long long)(int)dy && !((int)num == INT32_MIN))
+        q = (long long)((int)num / (int)dy);      // 32-bit fast path (always taken for on-screen geometry)
+    else
+        q = num / dy;
+    return (int)((long long)sx + q);
+}
+
+struct SortedTri { int x0, y0, x1, y1, x2, y2; };   // s0, s1, s2 of R:271 (y0 <= y1 <= y2)
+
+// interpolate(values: leftVertices, t:)  — the 3-point list [s0,s1,s2] (R:272, R:469-475)
+__device__ __forceinline__ int span_left(const SortedTri& s, int t) {
+    if (t >= s.y2) return s.x2;                           // R:470-471 + R:478-480: last row collapses to s2.x
+    if (t >= s.y1) return lerp_trunc(s.x1, s.y1, s.x2, s.y2, t);
+    return lerp_trunc(s.x0, s.y0, s.x1, s.y1, t);
+}
+// interpolate(values: rightVertices, t:) — the 2-point list [s0,s2] (R:273)
+__device__ __forceinline__ int span_right(const SortedTri& s, int t) {
+    if (s.y2 == s.y0) return s.x0;                        // R:486-488
+    return lerp_trunc(s.x0, s.y0, s.x2, s.y2, t);
+}
+// One row of R:275-283: returns inclusive [l, r] after the swap of R:278-280.
+__device__ __forceinline__ void span_row(const SortedTri& s, int t, int& l, int& r) {
+    int a = span_left(s, t), b = span_right(s, t);
+    l = min(a, b);
+    r = max(a, b);
+}
+
+// Stable insertion sort of 3 keys with strict < (Swift's sort on 3 elements, R:271).  Returns the permutation
+// as three 2-bit fields: perm = i0 | i1<<2 | i2<<4.
+__device__ __forceinline__ unsigned sort3_perm(float ya, float yb, float yc) {
+    int i0 = 0, i1 = 1, i2 = 2;
+    float k0 = ya, k1 = yb, k2 = yc;
+    if (k1 < k0) { float t = k0; k0 = k1; k1 = t; int u = i0; i0 = i1; i1 = u; }
+    if (k2 < k1) {
+        { float t = k1; k1 = k2; k2 = t; int u = i1; i1 = i2; i2 = u; }
+        if (k1 < k0) { float t = k0; k0 = k1; k1 = t; int u = i0; i0 = i1; i1 = u; }
+    }
+    return (unsigned)i0 | ((unsigned)i1 << 2) | ((unsigned)i2 << 4);
+}
+
+// ---- barycentric weights (R:88-100) ---------------------------------------------------------------------------
+struct BaryT { float c0x, c0y, c1x, c1y, cfx, cfy; };   // columns of T() = inverse, and cf
+
+// T() with the 2x2 inverse defined as adjugate / det, det and every quotient rounded separately, no singular
+// early-out (shared definition with oracle/; Apple's __invert_f2 is closed source).
+__device__ __forceinline__ BaryT bary_setup(int ax, int ay, int bx, int by, int cx, int cy) {
+    float afx = __fadd_rn(__int2float_rn(ax), 0.5f), afy = __fadd_rn(__int2float_rn(ay), 0.5f);
+    float bfx = __fadd_rn(__int2float_rn(bx), 0.5f), bfy = __fadd_rn(__int2float_rn(by), 0.5f);
+    float cfx = __fadd_rn(__int2float_rn(cx), 0.5f), cfy = __fadd_rn(__int2float_rn(cy), 0.5f);
+    float m00 = __fsub_rn(afx, cfx), m10 = __fsub_rn(afy, cfy);   // column 0
+    float m01 = __fsub_rn(bfx, cfx), m11 = __fsub_rn(bfy, cfy);   // column 1
+    float det = __fsub_rn(__fmul_rn(m00, m11), __fmul_rn(m01, m10));
+    BaryT t;
+    t.c0x = __fdiv_rn(m11, det);
+    t.c0y = __fdiv_rn(-m10, det);
+    t.c1x = __fdiv_rn(-m01, det);
+    t.c1y = __fdiv_rn(m00, det);
+    t.cfx = cfx;
+    t.cfy = cfy;
+    return t;
+}
+
+// ws(xy:) at the centre of pixel (x, y)  (R:252, R:88-93)
+__device__ __forceinline__ float3 bary_weights(const BaryT& t, int x, int y) {
+    float px = __fadd_rn(__int2float_rn(x), 0.5f), py = __fadd_rn(__int2float_rn(y), 0.5f);
+    float dx = __fsub_rn(px, t.cfx), dy = __fsub_rn(py, t.cfy);
+    float wa = __fadd_rn(__fmul_rn(t.c0x, dx), __fmul_rn(t.c1x, dy));
+    float wb = __fadd_rn(__fmul_rn(t.c0y, dx), __fmul_rn(t.c1y, dy));
+    return make_float3(wa, wb, __fsub_rn(__fsub_rn(1.0f, wa), wb));
+}
+
+// a*w.x + b*w.y + c*w.z, left to right, unfused (R:257, R:266)
+__device__ __forceinline__ float blend3(float a, float b, float c, float3 w) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(a, w.x), __fmul_rn(b, w.y)), __fmul_rn(c, w.z));
+}
+
+// Pixel(float3:) (R:117-128): clamp = fmin(fmax(v,0),1) (NaN -> 0), * 255, truncate; bytes b,g,r,a.
+__device__ __forceinline__ unsigned pack_bgra(float r, float g, float b) {
+    unsigned ub = (unsigned)__float2int_rz(__fmul_rn(fminf(fmaxf(b, 0.0f), 1.0f), 255.0f));
+    unsigned ug = (unsigned)__float2int_rz(__fmul_rn(fminf(fmaxf(g, 0.0f), 1.0f), 255.0f));
+    unsigned ur = (unsigned)__float2int_rz(__fmul_rn(fminf(fmaxf(r, 0.0f), 1.0f), 255.0f));
+    return ub | (ug << 8) | (ur << 16) | 0xFF000000u;
+}
+
+// ---- depth keys (SR_FLAG_DEPTH_LESS; R:257-261) ----------------------------------------------------------------
+// Sequential rule: a pixel keeps the smallest depth; among equal depths the earliest primitive (strict <).
+// key = monotone(depth) << 32 | prim, resolved with atomicMin.  NaN and +inf never pass `depth < +inf`.
+#define SR_KEY_EMPTY 0xFFFFFFFFFFFFFFFFull
+__device__ __forceinline__ bool depth_can_pass(float d) { return d < __int_as_float(0x7f800000); }
+__device__ __forceinline__ unsigned long long depth_key(float d, unsigned prim) {
+    unsigned u = __float_as_uint(d == 0.0f ? 0.0f : d);   // -0 and +0 compare equal in the reference's test
+    u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    return ((unsigned long long)u << 32) | prim;
+}
+
+}  // namespace sr

@@ -1,0 +1,260 @@
+"""Host-side mirror of the reference's render interface over the C ABI of libsr_cuda.so.
+
+The reference's seam is `Renderer.render(renderPass:)` (Renderer.swift:204-230; the Metal twin is
+GpuRenderer.swift:35).  `CudaRenderer.render(render_pass)` keeps that shape — same `RenderPass` fields
+(Renderer.swift:191-200), same `PrimitiveType` cases (Renderer.swift:174-189), caller-owned colour/depth images
+written in place (App.swift:80-101) — and forwards to the CUDA library through ctypes.  The Swift binding of the
+same ABI is under swift/ (it cannot be compiled in this image: no Swift toolchain).
+
+There is no CPU fallback: if libsr_cuda.so is missing, or no CUDA device is present, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import enum
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsr_cuda.so")
+
+SR_OK, SR_ERR_ARG, SR_ERR_INDEX, SR_ERR_DOMAIN, SR_ERR_CUDA, SR_ERR_NOMESH = 0, -1, -2, -3, -4, -5
+FLAG_DEPTH_LESS = 1 << 0
+FLAG_NO_DEPTH_OUT = 1 << 1
+
+#: every symbol include/sr_cuda.h declares
+ABI_SYMBOLS = (
+    "sr_version", "sr_create", "sr_destroy", "sr_last_error", "sr_set_mesh", "sr_render", "sr_render_pass",
+    "sr_render_batch", "sr_render_device", "sr_sync", "sr_get_stats", "sr_get_kernel_times", "sr_set_profiling",
+)
+
+
+class PrimitiveType(enum.IntEnum):
+    """Renderer.swift:174-189."""
+    triangle = 0
+    line = 1
+    vertices = 2
+
+    @property
+    def vertices_count(self) -> int:
+        return 2 if self is PrimitiveType.line else 3
+
+
+class SrStats(ctypes.Structure):
+    _fields_ = [
+        ("primitives", ctypes.c_uint64), ("domain_skipped", ctypes.c_uint64), ("small_tris", ctypes.c_uint64),
+        ("binned_tris", ctypes.c_uint64), ("tile_pairs", ctypes.c_uint64), ("bin_regrows", ctypes.c_uint64),
+        ("gpu_launches", ctypes.c_uint64), ("gpu_ms", ctypes.c_float),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class SrError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libsr_cuda error {code}: {message}")
+        self.code = code
+
+
+class DomainError(SrError):
+    """>= 1 primitive was skipped because a corner left the valid domain (the reference traps, Renderer.swift:251).
+    The frame was completed; the images hold everything else."""
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libsr_cuda.so (built in-tree by __graft_entry__.build()).  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback)")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, sz, i32, u32 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint32
+    L.sr_version.restype = i32
+    L.sr_version.argtypes = []
+    L.sr_create.restype = i32
+    L.sr_create.argtypes = [ctypes.POINTER(vp), i32]
+    L.sr_destroy.restype = None
+    L.sr_destroy.argtypes = [vp]
+    L.sr_last_error.restype = ctypes.c_char_p
+    L.sr_last_error.argtypes = [vp]
+    L.sr_set_mesh.restype = i32
+    L.sr_set_mesh.argtypes = [vp, vp, sz, vp, sz]
+    L.sr_render.restype = i32
+    L.sr_render.argtypes = [vp, vp, i32, i32, i32, vp, vp, u32]
+    L.sr_render_pass.restype = i32
+    L.sr_render_pass.argtypes = [vp, vp, sz, vp, sz, vp, i32, i32, i32, vp, vp, u32]
+    L.sr_render_batch.restype = i32
+    L.sr_render_batch.argtypes = [vp, vp, sz, i32, i32, i32, vp, vp, u32]
+    L.sr_render_device.restype = i32
+    L.sr_render_device.argtypes = [vp, vp, sz, i32, i32, i32, vp, vp, u32, vp]
+    L.sr_sync.restype = i32
+    L.sr_sync.argtypes = [vp]
+    L.sr_get_stats.restype = i32
+    L.sr_get_stats.argtypes = [vp, ctypes.POINTER(SrStats)]
+    L.sr_get_kernel_times.restype = i32
+    L.sr_get_kernel_times.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_float), i32]
+    L.sr_set_profiling.restype = i32
+    L.sr_set_profiling.argtypes = [vp, i32]
+    _lib = L
+    return L
+
+
+@dataclass
+class Image:
+    """Image<Pixel> (Renderer.swift:8-42): a non-owning view over caller memory, packed rows."""
+    array: np.ndarray   # colour: (H, W, 4) uint8 BGRA;  depth: (H, W) float32
+    width: int
+    height: int
+
+    @staticmethod
+    def color(width: int, height: int) -> "Image":
+        return Image(np.zeros((height, width, 4), dtype=np.uint8), width, height)
+
+    @staticmethod
+    def depth(width: int, height: int) -> "Image":
+        return Image(np.zeros((height, width), dtype=np.float32), width, height)
+
+
+@dataclass
+class RenderPass:
+    """Renderer.swift:191-200.  `vertices`: (N, 8) float32 rows x y z _ r g b _ (Swift Vertex, Renderer.swift:154-157);
+    `indices`: int64; `transform`: (4, 4) float32 in the M @ v sense (handed over column-major)."""
+    color_buffer: Image
+    depth_buffer: Image
+    vertices: np.ndarray
+    indices: np.ndarray
+    primitive_type: PrimitiveType = PrimitiveType.triangle
+    transform: np.ndarray = field(default_factory=lambda: np.eye(4, dtype=np.float32))
+
+
+def _colmajor(transform) -> np.ndarray:
+    m = np.asarray(transform, dtype=np.float32)
+    if m.ndim == 2:
+        return np.ascontiguousarray(m.T).reshape(16)
+    return np.ascontiguousarray(np.transpose(m, (0, 2, 1))).reshape(-1, 16)
+
+
+class CudaRenderer:
+    """Drop-in for `Renderer` / `GpuRenderer` (App.swift:148-154) on one B200."""
+
+    def __init__(self, device: int = 0):
+        self._lib = load_library()
+        self._ctx = ctypes.c_void_p()
+        rc = self._lib.sr_create(ctypes.byref(self._ctx), int(device))
+        if rc != SR_OK:
+            self._ctx = ctypes.c_void_p()
+            raise SrError(rc, "sr_create failed: no CUDA device / CUDA runtime error (there is no CPU fallback)")
+        self.device = device
+        self.depth_test = False      # True = run the depth test of Renderer.swift:257-261
+        self._mesh_key = None
+
+    # -- lifetime ----------------------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self._lib.sr_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- helpers -----------------------------------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc == SR_OK:
+            return
+        msg = (self._lib.sr_last_error(self._ctx) or b"").decode()
+        if rc == SR_ERR_DOMAIN:
+            raise DomainError(rc, f"{self.stats()['domain_skipped']} primitive(s) skipped by the domain rule")
+        raise SrError(rc, msg)
+
+    def _flags(self, want_depth: bool) -> int:
+        return (FLAG_DEPTH_LESS if self.depth_test else 0) | (0 if want_depth else FLAG_NO_DEPTH_OUT)
+
+    # -- mesh --------------------------------------------------------------------------------------------------
+    def set_mesh(self, vertices: np.ndarray, indices: np.ndarray):
+        v = np.ascontiguousarray(vertices, dtype=np.float32)
+        if v.ndim != 2 or v.shape[1] != 8:
+            raise ValueError("vertices must be (N, 8) float32 rows: x y z _ r g b _")
+        idx = np.ascontiguousarray(indices, dtype=np.int64).reshape(-1)
+        self._check(self._lib.sr_set_mesh(self._ctx, v.ctypes.data, v.shape[0], idx.ctypes.data, idx.shape[0]))
+        self._mesh_key = None
+
+    # -- render(renderPass:) -----------------------------------------------------------------------------------
+    def render(self, render_pass: RenderPass):
+        """Renderer.render(renderPass:) (Renderer.swift:204-230): synchronous, writes both images in place.
+        The mesh arrays travel with the pass, as in the reference (App.swift:163); they are re-uploaded only when
+        the array OBJECTS handed over are not the ones uploaded last; after modifying them in place call set_mesh."""
+        rp = render_pass
+        key = self._mesh_key
+        if key is None or key[0] is not rp.vertices or key[1] is not rp.indices:
+            self.set_mesh(rp.vertices, rp.indices)
+            self._mesh_key = (rp.vertices, rp.indices)     # strong refs: identity cannot be recycled
+        col, dep = rp.color_buffer.array, rp.depth_buffer.array
+        W, H = rp.color_buffer.width, rp.color_buffer.height
+        assert col.dtype == np.uint8 and col.flags.c_contiguous and col.size == W * H * 4
+        assert dep.dtype == np.float32 and dep.flags.c_contiguous and dep.size == W * H
+        m = _colmajor(rp.transform)
+        self._check(self._lib.sr_render(self._ctx, m.ctypes.data, int(rp.primitive_type), W, H,
+                                        col.ctypes.data, dep.ctypes.data, self._flags(True)))
+
+    def render_views(self, transforms, width: int, height: int, primitive_type=PrimitiveType.triangle,
+                     color_out: np.ndarray | None = None, depth_out: np.ndarray | None = None, want_depth=True):
+        """`n` independent render passes of the uploaded mesh.  Returns (color[n,H,W,4], depth[n,H,W] or None)."""
+        m = _colmajor(np.asarray(transforms, dtype=np.float32).reshape(-1, 4, 4))
+        n = m.shape[0]
+        color = color_out if color_out is not None else np.empty((n, height, width, 4), dtype=np.uint8)
+        depth = None
+        if want_depth:
+            depth = depth_out if depth_out is not None else np.empty((n, height, width), dtype=np.float32)
+        rc = self._lib.sr_render_batch(self._ctx, m.ctypes.data, n, int(primitive_type), width, height,
+                                       color.ctypes.data, depth.ctypes.data if depth is not None else None,
+                                       self._flags(want_depth))
+        self._check(rc)
+        return color, depth
+
+    def render_device(self, transforms, width: int, height: int, color_ptr: int, depth_ptr: int | None,
+                      primitive_type=PrimitiveType.triangle, stream: int | None = None, sync: bool = True):
+        """Device-resident variant: `color_ptr` / `depth_ptr` are CUDA device addresses (e.g. torch tensors'
+        data_ptr()) for n consecutive images; `stream` is a cudaStream_t handle or None."""
+        m = _colmajor(np.asarray(transforms, dtype=np.float32).reshape(-1, 4, 4))
+        rc = self._lib.sr_render_device(self._ctx, m.ctypes.data, m.shape[0], int(primitive_type), width, height,
+                                        ctypes.c_void_p(color_ptr), ctypes.c_void_p(depth_ptr) if depth_ptr else None,
+                                        self._flags(depth_ptr is not None), ctypes.c_void_p(stream) if stream else None)
+        self._check(rc)
+        if sync:
+            self.sync()
+
+    def sync(self):
+        self._check(self._lib.sr_sync(self._ctx))
+
+    # -- introspection -----------------------------------------------------------------------------------------
+    def stats(self) -> dict:
+        s = SrStats()
+        self._lib.sr_get_stats(self._ctx, ctypes.byref(s))
+        return s.as_dict()
+
+    def set_profiling(self, enabled: bool):
+        self._lib.sr_set_profiling(self._ctx, 1 if enabled else 0)
+
+    def kernel_times(self) -> dict:
+        names = (ctypes.c_char_p * 16)()
+        ms = (ctypes.c_float * 16)()
+        n = self._lib.sr_get_kernel_times(self._ctx, names, ms, 16)
+        return {names[i].decode(): float(ms[i]) for i in range(n)}

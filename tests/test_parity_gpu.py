@@ -1,0 +1,221 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the CPU oracle on the same inputs.
+Bar: coverage, depth and colour all bit-exact (integer/byte work; the float arithmetic is the same sequence of
+individually rounded operations on both sides)."""
+import numpy as np
+import pytest
+
+import software_renderer_b200 as srb
+from oracle import oracle as O
+from software_renderer_b200 import scene as S
+
+pytestmark = pytest.mark.gpu
+I4 = np.eye(4, dtype=np.float32)
+
+
+def gpu_render(r, v, i, m, W, H, prim=srb.PrimitiveType.triangle, depth_test=False, expect_domain=False):
+    r.depth_test = depth_test
+    rp = srb.RenderPass(srb.Image.color(W, H), srb.Image.depth(W, H), v, i, prim, m)
+    rp.color_buffer.array[:] = 0x5A      # stale contents must be overwritten (clear is part of the pass)
+    rp.depth_buffer.array[:] = -7.0
+    if expect_domain:
+        with pytest.raises(srb.DomainError):
+            r.render(rp)
+    else:
+        r.render(rp)
+    r.depth_test = False
+    return rp.color_buffer.array, rp.depth_buffer.array
+
+
+def assert_same(r, v, i, m, W, H, prim=srb.PrimitiveType.triangle, depth_test=False, expect_domain=False):
+    c, d = gpu_render(r, v, i, m, W, H, prim, depth_test, expect_domain)
+    flags = O.DEPTH_LESS if depth_test else 0
+    rc, rc_c, rc_d, st = O.render(v, i, m, W, H, primitive_type=int(prim), flags=flags)
+    assert rc == (O.ERR_DOMAIN if expect_domain else O.OK)
+    bad = (c != rc_c).any(-1)
+    assert not bad.any(), f"{int(bad.sum())} colour pixels differ, first at {np.argwhere(bad)[0]}"
+    assert np.array_equal(d.view(np.uint32), rc_d.view(np.uint32)), "depth differs"
+    return c, d, st
+
+
+def tri(xy):
+    xyz = np.array([[x, y, 0.0] for x, y in xy], np.float32)
+    return S.pack_vertices(xyz, np.eye(3, dtype=np.float32)), np.array([0, 1, 2], np.int64)
+
+
+def random_tris(seed, n, spread=1.3, zspread=(0.0, 1.0), small=None):
+    rng = np.random.default_rng(seed)
+    if small is None:
+        xyz = rng.uniform(-spread, spread, size=(3 * n, 3))
+    else:
+        c = rng.uniform(-spread, spread, size=(n, 1, 3))
+        xyz = (c + rng.uniform(-small, small, size=(n, 3, 3))).reshape(-1, 3)
+    xyz[:, 2] = rng.uniform(zspread[0], zspread[1], size=3 * n)
+    rgb = rng.uniform(-0.2, 1.2, size=(3 * n, 3))
+    return S.pack_vertices(xyz.astype(np.float32), rgb.astype(np.float32)), np.arange(3 * n, dtype=np.int64)
+
+
+def test_kat1_and_kat2(renderer):
+    v, i = tri([(0, 1), (1, 0), (-1, 0)])
+    c, d, st = assert_same(renderer, v, i, I4, 512, 512)
+    assert (c[..., 3] > 0).sum() == 65537
+    assert c[0, 256].tolist() == [0, 0, 255, 255] and c[128, 256].tolist() == [63, 63, 127, 255]
+    assert c[256, 0].tolist() == [255, 0, 0, 255] and c[100, 300].tolist() == [27, 71, 155, 255]
+    assert np.isposinf(d).all()
+    v, i = tri([(0, 0.5), (-0.5, -0.5), (0.5, -0.5)])
+    c, d, st = assert_same(renderer, v, i, I4, 512, 512)
+    assert np.nonzero(c[384, :, 3])[0].tolist() == [384]
+
+
+@pytest.mark.parametrize("depth_test", [False, True])
+@pytest.mark.parametrize("seed,n,size,kw", [
+    (1, 60, (97, 61), {}),                       # big triangles, odd image size (partial tiles)
+    (2, 400, (256, 256), {"small": 0.03}),       # small triangles: direct path
+    (3, 300, (640, 360), {"small": 0.15}),       # mixed
+    (4, 200, (333, 777), {"spread": 3.0}),       # mostly off-screen / partially clipped
+    (5, 2000, (800, 600), {"small": 0.004}),     # sub-pixel triangles (integer-degenerate -> NaN weights)
+    (6, 50, (1920, 1080), {}),                   # full-screen triangles, heavy overdraw
+])
+def test_random_triangles(renderer, seed, n, size, kw, depth_test):
+    v, i = random_tris(seed, n, **kw)
+    assert_same(renderer, v, i, I4, size[0], size[1], depth_test=depth_test)
+
+
+@pytest.mark.parametrize("depth_test", [False, True])
+def test_degenerate_and_tie_cases(renderer, depth_test):
+    # equal-y rows, coincident vertices, vertical slivers, exact depth ties between overlapping triangles
+    xy = [(-0.5, 0.0), (0.9, 0.0), (0.0, 0.0),   (0.2, 0.2), (0.2, 0.2), (0.2, 0.2),   (0.5, -0.9), (0.5, 0.9), (0.5, 0.1),
+          (-1, -1), (1, -1), (0, 1),   (-1, -1), (1, -1), (0, 1),   (1, 1), (-1, 1), (0, -1)]
+    xyz = np.array([[x, y, 0.5] for x, y in xy], np.float32)
+    rng = np.random.default_rng(0)
+    v = S.pack_vertices(xyz, rng.uniform(0, 1, size=(len(xy), 3)).astype(np.float32))
+    i = np.arange(len(xy), dtype=np.int64)
+    assert_same(renderer, v, i, I4, 200, 120, depth_test=depth_test)
+    assert_same(renderer, v, i[::-1].copy(), I4, 200, 120, depth_test=depth_test)
+
+
+def test_order_defines_visibility(renderer):
+    v, i = random_tris(11, 30)
+    c1, _, _ = assert_same(renderer, v, i, I4, 320, 200)
+    j = i.reshape(-1, 3)[::-1].reshape(-1).copy()
+    c2, _, _ = assert_same(renderer, v, j, I4, 320, 200)
+    assert not np.array_equal(c1, c2)
+
+
+@pytest.mark.parametrize("k", [0, 13, 47])
+def test_config1_cube_800x600(renderer, k):
+    v, i = S.cube()
+    assert_same(renderer, v, i, S.app_transform(k / 60), 800, 600)
+    assert_same(renderer, v, i, S.app_transform(k / 60), 800, 600, depth_test=True)
+
+
+@pytest.mark.parametrize("depth_test", [False, True])
+def test_config2_icosphere_1080p(renderer, depth_test):
+    v, i = S.icosphere(6)
+    c, d, st = assert_same(renderer, v, i, S.app_transform(0.5), 1920, 1080, depth_test=depth_test)
+    assert st["primitives"] == 81920
+
+
+@pytest.mark.parametrize("depth_test", [False, True])
+def test_config3_soup_reduced(renderer, depth_test):
+    v, i = S.triangle_soup(60_000, 1920, 1080, seed=3)
+    assert_same(renderer, v, i, S.soup_transform(2), 1920, 1080, depth_test=depth_test)
+
+
+def test_config3_soup_full_1m(renderer):
+    v, i = S.triangle_soup(1_000_000, 1920, 1080)
+    c, d, st = assert_same(renderer, v, i, S.soup_transform(0), 1920, 1080)
+    assert (c[..., 3] > 0).all()
+    s = renderer.stats()
+    assert s["small_tris"] + s["binned_tris"] <= 1_000_000 and s["binned_tris"] > 100_000
+
+
+def test_config5_cubesphere_512_views(renderer):
+    v, i = S.cube_sphere(289)
+    views = S.fibonacci_views(4096)[[0, 1000, 4095]]
+    renderer.set_mesh(v, i)
+    color, depth = renderer.render_views(views, 512, 512)
+    for k in range(3):
+        rc, rc_c, rc_d, _ = O.render(v, i, views[k], 512, 512)
+        assert rc == 0 and np.array_equal(color[k], rc_c) and np.array_equal(depth[k], rc_d)
+
+
+def test_config4_cubesphere_10m_4k_properties(renderer):
+    """Full size of configs[3]: the oracle needs ~10 s here, so one frame is compared directly."""
+    v, i = S.cube_sphere(913)
+    assert i.size // 3 == 10_002_828
+    m = S.app_transform(0.25)
+    assert_same(renderer, v, i, m, 3840, 2160)
+
+
+def test_vertices_and_line_primitives(renderer):
+    v, i = random_tris(21, 500, spread=1.2)
+    assert_same(renderer, v, i, I4, 300, 200, prim=srb.PrimitiveType.vertices)
+    c, d, _ = assert_same(renderer, v, i, I4, 300, 200, prim=srb.PrimitiveType.line)
+    assert not c.any()
+    # collisions: many corners on one pixel -> the last corner wins
+    xyz = np.zeros((30, 3), np.float32)
+    rgb = np.random.default_rng(5).uniform(0, 1, size=(30, 3)).astype(np.float32)
+    assert_same(renderer, S.pack_vertices(xyz, rgb), np.arange(30, dtype=np.int64), I4, 64, 64, prim=srb.PrimitiveType.vertices)
+
+
+def test_domain_rule_and_index_errors(renderer):
+    v, i = random_tris(31, 40)
+    v[5, 0] = np.inf
+    v[40, 1] = np.nan
+    v[77, 0] = 3e9           # |sx| >= 2^30
+    assert_same(renderer, v, i, I4, 128, 128, expect_domain=True)
+    assert renderer.stats()["domain_skipped"] == 3
+    assert_same(renderer, v, i, I4, 128, 128, prim=srb.PrimitiveType.vertices, expect_domain=True)
+    m = I4.copy()
+    m[3, 3] = 0.0            # w = 0 for every vertex
+    assert_same(renderer, *random_tris(32, 10), m, 64, 64, expect_domain=True)
+    bad = i.copy()
+    bad[10] = v.shape[0]
+    with pytest.raises(srb.SrError) as e:
+        gpu_render(renderer, v, bad, I4, 64, 64)
+    assert e.value.code == -2
+    ok_trailing = np.concatenate([np.arange(6), [10 ** 9]]).astype(np.int64)   # partial primitive is ignored
+    assert_same(renderer, *random_tris(33, 2)[:1], ok_trailing, I4, 64, 64)
+
+
+def test_empty_mesh_is_a_clear(renderer):
+    v = np.zeros((0, 8), np.float32)
+    i = np.zeros((0,), np.int64)
+    c, d, _ = assert_same(renderer, v, i, I4, 50, 40)
+    assert not c.any() and np.isposinf(d).all()
+
+
+def test_batch_equals_single_and_device_path(renderer):
+    import torch
+    v, i = S.icosphere(4)
+    views = S.fibonacci_views(16)
+    renderer.set_mesh(v, i)
+    color, depth = renderer.render_views(views, 256, 192)
+    dev_c = torch.empty((16, 192, 256, 4), dtype=torch.uint8, device="cuda")
+    dev_d = torch.empty((16, 192, 256), dtype=torch.float32, device="cuda")
+    renderer.render_device(views, 256, 192, dev_c.data_ptr(), dev_d.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
+    assert np.array_equal(dev_c.cpu().numpy(), color) and np.array_equal(dev_d.cpu().numpy(), depth)
+    for k in (0, 7, 15):
+        rc, rc_c, rc_d, _ = O.render(v, i, views[k], 256, 192)
+        assert np.array_equal(color[k], rc_c) and np.array_equal(depth[k], rc_d)
+
+
+def test_pair_buffer_regrow(renderer):
+    """Many full-screen triangles overflow the initial tile-list buffer; the frame is re-run and still exact."""
+    r = srb.CudaRenderer(0)
+    try:
+        v, i = random_tris(41, 400, spread=1.5)
+        c, d = gpu_render(r, v, i, I4, 1920, 1080)
+        rc, rc_c, rc_d, _ = O.render(v, i, I4, 1920, 1080)
+        assert np.array_equal(c, rc_c) and np.array_equal(d, rc_d)
+        assert r.stats()["tile_pairs"] > (1 << 20) and r.stats()["bin_regrows"] >= 1
+    finally:
+        r.close()
+
+
+def test_repeatability_and_self_clearing(renderer):
+    v, i = random_tris(51, 200, small=0.2)
+    a = [gpu_render(renderer, v, i, S.app_transform(t), 400, 300, depth_test=dt) for t in (0.1, 0.2) for dt in (False, True)]
+    b = [gpu_render(renderer, v, i, S.app_transform(t), 400, 300, depth_test=dt) for t in (0.1, 0.2) for dt in (False, True)]
+    for (c1, d1), (c2, d2) in zip(a, b):
+        assert np.array_equal(c1, c2) and np.array_equal(d1, d2)
