@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""bench.py — frames/s of the rasterization hot path (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload soup1m|ico80k|cs10m4k|views512] [--impl reference]
+
+A "step" is one render pass (Renderer.render(renderPass:), Renderer.swift:204-230) of the named workload with that
+step's own transform.  Default workload: BASELINE.json's metric config — 1M-triangle soup at 1920x1080 (configs[2]).
+  value  frames/s, whole job, mesh resident in HBM, images left in HBM; device time from CUDA events on the launching
+         stream; L2 flushed between timed frames; max over ranks.
+  e2e    same metric through the synchronous host-pointer C-ABI call (sr_render): per step the transform goes in and
+         the colour and depth images come back to pinned host memory inside the timed region.
+  --impl reference   the CPU restatement of the reference path (oracle/, the reference itself is Swift and cannot be
+         built here) on all host cores, one bounded sample of the same workload per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (description, width, height)
+    "soup1m": ("1M-triangle random soup, heavy overdraw, 1920x1080 (BASELINE.json configs[2])", 1920, 1080),
+    "ico80k": ("icosphere subdiv 6 (81,920 tris), baked Lambert, 1920x1080 (configs[1])", 1920, 1080),
+    "cs10m4k": ("cube-sphere n=913 (10,002,828 tris), 3840x2160 (configs[3])", 3840, 2160),
+    "views512": ("cube-sphere n=289 (1,002,252 tris), 512x512 camera views (configs[4])", 512, 512),
+}
+
+
+def make_workload(name: str):
+    from software_renderer_b200 import scene as S
+    desc, W, H = WORKLOADS[name]
+    if name == "soup1m":
+        v, i = S.triangle_soup(1_000_000, W, H)
+        xf = S.soup_transform
+    elif name == "ico80k":
+        v, i = S.icosphere(6)
+        xf = lambda k: S.app_transform(k / 60.0)
+    elif name == "cs10m4k":
+        v, i = S.cube_sphere(913)
+        xf = lambda k: S.app_transform(k / 60.0)
+    else:
+        v, i = S.cube_sphere(289)
+        views = S.fibonacci_views(4096)
+        xf = lambda k: views[k % 4096]
+    return desc, W, H, v, i, xf
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons (NVML) during the timed region."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            pass
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_count() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def time_oracle(v, i, xf, W, H, nthreads: int, frames_per_thread: int, stride: int):
+    """Runs the oracle on `nthreads` host threads, each rendering `frames_per_thread` samples (every `stride`-th
+    triangle of the frame).  Returns seconds of wall time."""
+    from oracle import oracle as O
+    O.lib()
+    idx = np.ascontiguousarray(i.reshape(-1, 3)[::stride].reshape(-1))
+    bufs = [(np.empty((H, W, 4), np.uint8), np.empty((H, W), np.float32)) for _ in range(nthreads)]
+
+    def work(t):
+        for f in range(frames_per_thread):
+            O.render(v, idx, xf(t * frames_per_thread + f), W, H, color_out=bufs[t][0], depth_out=bufs[t][1])
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(nthreads)]
+    t0 = time.perf_counter()
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """Reference arm: the CPU restatement (oracle/) on all host cores; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    desc, W, H, v, i, xf = make_workload(args.workload)
+    ntris = i.size // 3
+    cores = cpu_count()
+    from oracle import oracle as O
+    O.lib()
+    # calibrate: one thread, a 1/64 sample of one frame
+    stride0 = 64 if ntris >= 64_000 else 1
+    t_cal = time_oracle(v, i, xf, W, H, 1, 1, stride0)
+    full_frame_s = t_cal * stride0                       # estimate; cost is ~linear in triangles for these meshes
+    budget = 150.0 / max(1, args.steps + args.warmup)    # seconds per step
+    stride = 1
+    while full_frame_s / stride > budget and ntris // (stride * 2) >= 1000:
+        stride *= 2
+    for _ in range(args.warmup):
+        time_oracle(v, i, xf, W, H, cores, 1, stride)
+    t = 0.0
+    for _ in range(args.steps):
+        t += time_oracle(v, i, xf, W, H, cores, 1, stride)
+    # each step renders `cores` samples, each 1/stride of a frame's triangles (plus a full clear)
+    frames = args.steps * cores / stride
+    value = frames / t
+    sample = (f"each step = {cores} host threads x 1 render pass of every {stride}-th triangle of the frame "
+              f"({ntris // stride} of {ntris} tris, full {W}x{H} clear); frames counted as 1/{stride} each")
+    line = {
+        "impl": "reference", "metric": "frames_per_second", "value": value, "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * t / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+i64", "data": "synthetic",
+        "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": int(v.shape[0])},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference is Swift (no toolchain here): oracle/ C++ restatement of Renderer.swift, -O2 -ffp-contract=off",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    import software_renderer_b200 as srb
+    from software_renderer_b200 import scene as S
+    from software_renderer_b200.multi_gpu import max_over_ranks
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    desc, W, H, v, i, xf = make_workload(args.workload)
+    ntris, nverts = i.size // 3, int(v.shape[0])
+    K, Wm = args.steps, args.warmup
+    r = srb.CudaRenderer(local)
+    r.depth_test = bool(args.depth_test)
+    r.set_mesh(v, i)
+    stream = torch.cuda.Stream(device=dev)
+    color = torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
+    depth = torch.empty((H, W), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+    # every rank renders its own frames: frame index = rank * (K + Wm) + step
+    frame0 = rank * (K + Wm + 8)
+
+    def frame(k):
+        r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream, sync=False)
+
+    with torch.cuda.stream(stream):
+        for k in range(Wm):
+            frame(k)
+        r.sync()
+        launches_before = None
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        t_wall0 = time.perf_counter()
+        launches = 0
+        for k in range(K):
+            flush.fill_(k & 0xFF)                       # L2 flush between timed frames (not timed)
+            evs[k][0].record(stream)
+            frame(Wm + k)
+            evs[k][1].record(stream)
+            r.sync()                                    # status read-back; outside the event pair
+            launches += r.stats()["gpu_launches"]
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        t_wall = time.perf_counter() - t_wall0
+        clocks = sampler.stop()
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    dev_ms = max_over_ranks(dev_ms, device=dev)
+    value = world * K / (dev_ms / 1000.0)
+
+    # ---- e2e: synchronous host-pointer C-ABI call, pinned host images ------------------------------------------
+    hc = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    hd = torch.empty((H, W), dtype=torch.float32).pin_memory()
+    rp = srb.RenderPass(srb.Image(hc.numpy(), W, H), srb.Image(hd.numpy(), W, H), v, i, srb.PrimitiveType.triangle, None)
+    r._mesh_key = (v, i)                                # mesh already uploaded (static across frames)
+    for k in range(max(3, Wm)):
+        rp.transform = xf(frame0 + k)
+        r.render(rp)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for k in range(K):
+        rp.transform = xf(frame0 + Wm + k)
+        r.render(rp)
+    t_e2e = time.perf_counter() - t0
+    t_e2e = max_over_ranks(t_e2e, device=dev)
+    e2e_value = world * K / t_e2e
+
+    line = None
+    if rank == 0:
+        # per-kernel split of one frame (extra events between kernels; separate from the timed loop)
+        r.set_profiling(True)
+        acc = {}
+        reps = 5
+        for k in range(reps):
+            flush.fill_(1)
+            torch.cuda.synchronize(dev)
+            r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream)
+            for nm, ms in r.kernel_times().items():
+                acc[nm] = acc.get(nm, 0.0) + ms / reps
+        r.set_profiling(False)
+        stats = r.stats()
+        hbm, peak_kind = peaks()
+        # algorithmic bytes: indices 12 B/tri, vertex xyz+rgb 24 B, colour+depth 8 B/pixel, split over
+        # the kernels that touch them
+        alg = {"k_transform": 12 * nverts, "k_setup": 12 * ntris, "k_tile": 12 * nverts + 8 * W * H}
+        top = max(acc, key=acc.get) if acc else "k_tile"
+        top_ms = acc.get(top, float("nan"))
+        top_bytes = alg.get(top, 0)
+        achieved = top_bytes / (top_ms * 1e-3) / 1e9 if top_ms and top_ms == top_ms else float("nan")
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get(args.workload, {}).get(top)
+            except Exception:
+                traffic = None
+        frame_bytes = S.algorithmic_bytes(ntris, nverts, W, H)
+        frame_ms = dev_ms / K
+        # CPU baseline: the oracle on one host core (the reference loop is sequential, Renderer.swift:222)
+        stride = 8 if ntris >= 500_000 else 1
+        t_cpu = time_oracle(v, i, xf, W, H, 1, 1, stride)
+        cpu_value = (1.0 / stride) / t_cpu
+        line = {
+            "metric": "frames_per_second", "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32+i64", "data": "synthetic",
+            "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": nverts,
+                       "depth_test": bool(args.depth_test), "l2": "flushed between timed frames (256 MiB fill)",
+                       "parallelism": f"{world} independent view streams, one per GPU"},
+            "gtri_per_s": value * ntris / 1e9,
+            "frame_roofline": {"bound": "hbm", "achieved": frame_bytes / (frame_ms * 1e-3) / 1e9, "peak": hbm,
+                               "unit": "GB/s", "frac": frame_bytes / (frame_ms * 1e-3) / 1e9 / hbm,
+                               "bytes_per_frame": frame_bytes, "peak_kind": peak_kind},
+            "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s",
+                         "frac": achieved / hbm, "traffic": traffic, "algorithmic_bytes": top_bytes,
+                         "kernel_ms": top_ms, "peak_kind": peak_kind},
+            "kernel_ms": acc,
+            "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": 1, "kind": "port",
+                             "sample": f"1 render pass of every {stride}-th triangle ({ntris // stride} tris) on 1 core, "
+                                       f"{t_cpu:.2f} s, scaled x{stride}; host has {cpu_count()} cores"},
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": 8 * W * H,
+                    "api": "sr_render (synchronous, pinned host images; mesh uploaded once by sr_set_mesh)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "wall_s_timed_region": t_wall,
+            "stats_last_frame": {k: (int(x) if k != "gpu_ms" else float(x)) for k, x in stats.items()},
+        }
+    r.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--workload", default="soup1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--depth-test", type=int, default=0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()
