@@ -1,0 +1,95 @@
+// sr_renderer.hpp — C++ host-side mirror of the reference's render interface over the C ABI (sr_cuda.h).
+//
+// The reference's host language is Swift; this image has no Swift toolchain, so the compiled-language host side is
+// C++ (header-only).  Names and argument meaning follow Renderer.swift:
+//   sr::Vertex         Renderer.swift:154-157      sr::PrimitiveType  Renderer.swift:174-189
+//   sr::Pixel          Renderer.swift:44-49        sr::Image<T>       Renderer.swift:8-42
+//   sr::RenderPass     Renderer.swift:191-200      sr::CudaRenderer::render(const RenderPass&)  Renderer.swift:204
+// Error behaviour: where the reference traps (bad index R:226, NaN/inf corner R:251) render() throws
+// std::runtime_error / returns the count of skipped primitives; it never falls back to the CPU.
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "sr_cuda.h"
+
+namespace sr {
+
+struct float3 { float x, y, z, _pad; };                    // SIMD3<Float>: 16 bytes
+struct Vertex { float3 xyz; float3 color; };               // 32 bytes
+static_assert(sizeof(Vertex) == sizeof(sr_vertex), "Vertex must match Swift's layout");
+
+struct Pixel { uint8_t b, g, r, a; };
+
+enum class PrimitiveType : int { triangle = SR_TRIANGLE, line = SR_LINE, vertices = SR_VERTICES };
+inline int verticesCount(PrimitiveType p) { return p == PrimitiveType::line ? 2 : 3; }
+
+template <class T>
+struct Image {                                             // non-owning view over caller memory
+    T* pointer;
+    int width, height, bytesPerRow;
+};
+using ColorImage = Image<Pixel>;
+using DepthImage = Image<float>;
+
+struct matrix_float4x4 {                                   // column-major, 64 bytes
+    float columns[4][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}};
+};
+
+struct RenderPass {
+    ColorImage colorBuffer;
+    DepthImage depthBuffer;
+    std::vector<Vertex> vertices;
+    std::vector<int64_t> indices;                          // Swift [Int]
+    PrimitiveType primitiveType = PrimitiveType::triangle;
+    matrix_float4x4 transform;
+};
+
+class CudaRenderer {
+public:
+    explicit CudaRenderer(int device = 0) {
+        int rc = sr_create(&ctx_, device);
+        if (rc != SR_OK) throw std::runtime_error("sr_create failed (no CUDA device; there is no CPU fallback): " + std::to_string(rc));
+    }
+    ~CudaRenderer() { sr_destroy(ctx_); }
+    CudaRenderer(const CudaRenderer&) = delete;
+    CudaRenderer& operator=(const CudaRenderer&) = delete;
+
+    bool depthTest = false;                                // true: the test commented out at Renderer.swift:257-261
+
+    // Uploads the mesh of the pass (the reference hands the arrays over on every call, App.swift:163).
+    void setMesh(const std::vector<Vertex>& v, const std::vector<int64_t>& i) {
+        check(sr_set_mesh(ctx_, reinterpret_cast<const sr_vertex*>(v.data()), v.size(), i.data(), i.size()));
+        mesh_v_ = v.data(); mesh_i_ = i.data(); mesh_nv_ = v.size(); mesh_ni_ = i.size();
+    }
+
+    // render(renderPass:) — synchronous; writes colorBuffer and depthBuffer in place.  Returns the number of
+    // primitives skipped by the domain rule (0 for every input the reference itself can render).
+    uint64_t render(const RenderPass& rp) {
+        if (rp.vertices.data() != mesh_v_ || rp.indices.data() != mesh_i_ || rp.vertices.size() != mesh_nv_ || rp.indices.size() != mesh_ni_)
+            setMesh(rp.vertices, rp.indices);
+        int rc = sr_render(ctx_, &rp.transform.columns[0][0], static_cast<int>(rp.primitiveType), rp.colorBuffer.width,
+                           rp.colorBuffer.height, reinterpret_cast<uint8_t*>(rp.colorBuffer.pointer), rp.depthBuffer.pointer,
+                           depthTest ? SR_FLAG_DEPTH_LESS : 0u);
+        sr_stats st{};
+        sr_get_stats(ctx_, &st);
+        if (rc != SR_OK && rc != SR_ERR_DOMAIN) check(rc);
+        return st.domain_skipped;
+    }
+
+    sr_stats stats() const { sr_stats st{}; sr_get_stats(ctx_, &st); return st; }
+    sr_ctx* raw() const { return ctx_; }
+
+private:
+    void check(int rc) const {
+        if (rc != SR_OK) throw std::runtime_error(std::string("libsr_cuda: ") + sr_last_error(ctx_) + " (" + std::to_string(rc) + ")");
+    }
+    sr_ctx* ctx_ = nullptr;
+    const void* mesh_v_ = nullptr;
+    const void* mesh_i_ = nullptr;
+    size_t mesh_nv_ = 0, mesh_ni_ = 0;
+};
+
+}  // namespace sr

@@ -1,0 +1,98 @@
+// CudaRenderer.swift — drop-in for `Renderer` / `GpuRenderer`: same `render(renderPass:)` entry point over the same
+// RenderPass / Vertex / PrimitiveType / Image types (Renderer.swift:8-49, 154-200 in the reference).  The caller picks
+// the implementation by assignment (App.swift:154):   let renderer = cudaRenderer
+// UNVERIFIED: this file cannot be compiled in this repository's image (no Swift toolchain).  The C ABI it binds is
+// exercised by tests/ through ctypes.
+import CSRCuda
+
+public typealias ColorImage = Image<Pixel>
+public typealias DepthImage = Image<Float>
+
+/// Renderer.swift:8-42 without the two Metal-only optionals (texture, buffer).
+public final class Image<P> {
+    public init(pointer: UnsafeMutablePointer<P>, width: Int, height: Int, bytesPerRow: Int) {
+        self.pointer = pointer; self.width = width; self.height = height; self.bytesPerRow = bytesPerRow
+    }
+    public private(set) var pointer: UnsafeMutablePointer<P>
+    public let width: Int, height: Int, bytesPerRow: Int
+}
+
+/// Renderer.swift:44-49
+public struct Pixel { public var b: UInt8, g: UInt8, r: UInt8, a: UInt8 }
+
+/// Renderer.swift:154-157 — two SIMD3<Float>: 32 bytes, the layout sr_vertex mirrors.
+public struct Vertex {
+    public let xyz: vector_float3
+    public let color: vector_float3
+    public init(xyz: vector_float3, color: vector_float3) { self.xyz = xyz; self.color = color }
+}
+
+/// Renderer.swift:174-189
+public enum PrimitiveType {
+    case triangle, line, vertices
+    var raw: Int32 { switch self { case .triangle: return 0; case .line: return 1; case .vertices: return 2 } }
+}
+
+/// Renderer.swift:191-200
+public struct RenderPass {
+    public var colorBuffer: ColorImage
+    public var depthBuffer: DepthImage
+    public var vertices: [Vertex]
+    public var indices: [Int]
+    public var primitiveType: PrimitiveType = .triangle
+    public var transform: matrix_float4x4 = .init(diagonal: .init(1, 1, 1, 1))
+    public init(colorBuffer: ColorImage, depthBuffer: DepthImage, vertices: [Vertex], indices: [Int]) {
+        self.colorBuffer = colorBuffer; self.depthBuffer = depthBuffer; self.vertices = vertices; self.indices = indices
+    }
+}
+
+public enum CudaRendererError: Error { case create(Int32), render(Int32, String) }
+
+public final class CudaRenderer {
+    private var ctx: OpaquePointer?
+    /// true = run the depth test that is commented out at Renderer.swift:257-261
+    public var depthTest = false
+    /// Set when the last pass skipped primitives outside the valid domain (the reference would have trapped).
+    public private(set) var lastDomainSkips: UInt64 = 0
+    // the arrays of the previous pass: re-upload only when they change (GpuRenderer caches by length, G:41-67)
+    private var meshCount: (Int, Int) = (-1, -1)
+    private var meshHash: Int = 0
+
+    public init(device: Int32 = 0) throws {
+        precondition(MemoryLayout<Vertex>.stride == 32 && MemoryLayout<Int>.size == 8)
+        let rc = sr_create(&ctx, device)
+        guard rc == 0 else { throw CudaRendererError.create(rc) }   // no CPU fallback
+    }
+    deinit { sr_destroy(ctx) }
+
+    /// Same signature and contract as Renderer.render(renderPass:) (Renderer.swift:204): synchronous, writes
+    /// colorBuffer and depthBuffer in place.
+    public func render(renderPass: RenderPass) {
+        let w = Int32(renderPass.colorBuffer.width), h = Int32(renderPass.colorBuffer.height)
+        var hasher = Hasher()
+        renderPass.vertices.withUnsafeBytes { hasher.combine(bytes: $0) }
+        renderPass.indices.withUnsafeBytes { hasher.combine(bytes: $0) }
+        let hash = hasher.finalize()
+        if meshCount != (renderPass.vertices.count, renderPass.indices.count) || hash != meshHash {
+            let rc = renderPass.vertices.withUnsafeBytes { vb in
+                renderPass.indices.withUnsafeBufferPointer { ib in
+                    sr_set_mesh(ctx, vb.baseAddress?.assumingMemoryBound(to: sr_vertex.self), renderPass.vertices.count,
+                                UnsafeRawPointer(ib.baseAddress)?.assumingMemoryBound(to: Int64.self), renderPass.indices.count)
+                }
+            }
+            precondition(rc == 0, String(cString: sr_last_error(ctx)))   // Renderer.swift:226 traps on a bad index
+            meshCount = (renderPass.vertices.count, renderPass.indices.count); meshHash = hash
+        }
+        var m = renderPass.transform
+        let flags: UInt32 = depthTest ? UInt32(SR_FLAG_DEPTH_LESS) : 0
+        let rc = withUnsafeBytes(of: &m) { mb in
+            sr_render(ctx, mb.baseAddress!.assumingMemoryBound(to: Float.self), renderPass.primitiveType.raw, w, h,
+                      UnsafeMutableRawPointer(renderPass.colorBuffer.pointer).assumingMemoryBound(to: UInt8.self),
+                      renderPass.depthBuffer.pointer, flags)
+        }
+        var st = sr_stats()
+        sr_get_stats(ctx, &st)
+        lastDomainSkips = st.domain_skipped
+        precondition(rc == 0 || rc == SR_ERR_DOMAIN.rawValue, String(cString: sr_last_error(ctx)))
+    }
+}

@@ -1,0 +1,75 @@
+"""Host-side logic of the N>1 path on CPU: world_size-2 gloo processes shard a view list, "render" their shard with the
+oracle (the CUDA library needs a GPU), and gather the framebuffers to rank 0 exactly as bench.py / the GPU box does
+with NCCL.  The gathered composite must equal the single-process result."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from software_renderer_b200 import scene as S  # noqa: E402
+from software_renderer_b200.multi_gpu import gather_framebuffers, max_over_ranks, shard_range  # noqa: E402
+
+NVIEWS, W, H = 5, 96, 64
+
+
+def test_shard_range_partitions_exactly():
+    for n in (0, 1, 5, 8, 4096, 4097):
+        for world in (1, 2, 3, 4, 8):
+            spans = [shard_range(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            for a, b in zip(spans, spans[1:]):
+                assert a[1] == b[0]
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        shard_range(4, 2, 2)
+
+
+def _render_views(views):
+    from oracle import oracle as O
+    v, i = S.icosphere(2)
+    out = np.empty((len(views), H, W, 4), np.uint8)
+    for k, m in enumerate(views):
+        rc, c, _, _ = O.render(v, i, m, W, H)
+        assert rc == 0
+        out[k] = c
+    return out
+
+
+def _worker(rank, world, port, result_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        views = S.fibonacci_views(NVIEWS)
+        lo, hi = shard_range(NVIEWS, rank, world)
+        local = torch.from_numpy(_render_views(views[lo:hi]))
+        full = gather_framebuffers(local, NVIEWS, dst=0)
+        t = max_over_ranks(float(rank + 1))
+        assert t == float(world)
+        if rank == 0:
+            np.save(result_path, full.numpy())
+        else:
+            assert full is None
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_views_gather_equals_single_process(tmp_path):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    path = str(tmp_path / "composite.npy")
+    mp.spawn(_worker, args=(2, port, path), nprocs=2, join=True)
+    got = np.load(path)
+    want = _render_views(S.fibonacci_views(NVIEWS))
+    assert got.shape == want.shape and np.array_equal(got, want)
