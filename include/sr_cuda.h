@@ -70,6 +70,8 @@ typedef struct sr_stats {
     uint64_t binned_tris;     /* triangles sent through tile binning */
     uint64_t tile_pairs;      /* (triangle, tile) pairs produced by binning */
     uint64_t bin_regrows;     /* times a frame was re-run because the pair buffer had to grow */
+    uint64_t pairs_consumed;  /* pairs the tile kernel read before its exact early-out */
+    uint64_t batches_run;     /* index-descending batches that still had open tiles (0 = single-batch frame) */
     uint64_t gpu_launches;    /* kernels launched by the call */
     float    gpu_ms;          /* device time of the call's kernels, CUDA events on the context's stream */
 } sr_stats;

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -13,7 +14,7 @@ using namespace sr;
 
 namespace {
 
-constexpr int MAX_PROF = 16;
+constexpr int MAX_PROF = 64;
 
 template <class T>
 struct DevBuf {
@@ -55,6 +56,11 @@ struct sr_ctx {
     DevBuf<unsigned long long> look;        // scan look-back array
     DevBuf<unsigned> ticket;
     unsigned ticket_base = 0, epoch = 0;
+    DevBuf<unsigned> tile_done;             // frame stamp of tiles retired early (batched mode)
+    unsigned frame_epoch = 0;
+    // adaptive policy (depth off): index-descending batches pay off when most tile-list entries are never read
+    bool batched_mode = false;
+    int force_batches = -1;                 // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     DevBuf<ViewStatus> status;
     ViewStatus* h_status = nullptr;
     size_t h_status_cap = 0;
@@ -131,6 +137,11 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
         SR_CUDA(c, cudaMemsetAsync(c->counts.p, 0, ncnt * sizeof(unsigned), st));
     }
     SR_CUDA(c, c->cursor.reserve(ncnt));
+    if (tiles > c->tile_done.cap) {
+        SR_CUDA(c, c->tile_done.reserve(tiles));
+        SR_CUDA(c, cudaMemsetAsync(c->tile_done.p, 0, tiles * sizeof(unsigned), st));
+        c->frame_epoch = 0;
+    }
     const size_t nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
     if (nblocks > c->look.cap) {
         SR_CUDA(c, c->look.reserve(nblocks));
@@ -185,38 +196,52 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         c->launches++;
     }
     if (prim == SR_TRIANGLE) {
+        const int ntris = (int)(c->nidx / 3);
         FrameParams fp;
         fp.width = W; fp.height = H;
         fp.tiles_x = (int)div_up(W, TILE); fp.tiles_y = (int)div_up(H, TILE);
-        fp.ntris = (int)(c->nidx / 3);
-        fp.chunk_shift = 0;
-        while (fp.ntris > 0 && ((fp.ntris - 1) >> fp.chunk_shift) >= NCHUNK) fp.chunk_shift++;
+        fp.ntiles = fp.tiles_x * fp.tiles_y;
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
-        const int ntiles = fp.tiles_x * fp.tiles_y;
-        const int ncnt = ntiles * NCHUNK;
-        if (fp.ntris > 0) {
-            prof_mark(c, st, "k_setup");
-            if (depth_mode) k_setup<true><<<div_up(fp.ntris, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, d_status);
-            else            k_setup<false><<<div_up(fp.ntris, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, d_status);
-            c->launches++;
-        }
-        const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
-        c->epoch++;
-        prof_mark(c, st, "k_scan");
-        k_scan<<<nblocks, SCAN_THREADS, 0, st>>>(c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, d_status);
-        c->ticket_base += nblocks;
-        c->launches++;
-        if (fp.ntris > 0) {
-            prof_mark(c, st, "k_bin_fill");
-            const unsigned grid = std::min<unsigned>(div_up(fp.ntris, 256), 148 * 8);
-            k_bin_fill<<<grid, 256, 0, st>>>(c->recs.p, d_status, fp, c->cursor.p, c->pairs.p);
-            c->launches++;
+        fp.epoch = ++c->frame_epoch;
+        fp.batched = (!depth_mode && c->batched_mode && ntris >= (1 << 16)) ? 1 : 0;
+        const int ncnt = fp.ntiles * NCHUNK;
+        // index-descending batches: T/16, T/16, T/8, T/4, T/2 from the top; one batch otherwise
+        BatchParams batches[MAX_BATCHES];
+        int nb = 0;
+        if (fp.batched) {
+            const int cuts[6] = {ntris, ntris - ntris / 16, ntris - ntris / 8, ntris - ntris / 4, ntris / 2, 0};
+            for (int b = 0; b < 5; ++b) batches[nb++] = BatchParams{cuts[b + 1], cuts[b], 0, b, b == 4};
+        } else {
+            batches[nb++] = BatchParams{0, ntris, 0, 0, 1};
         }
         ShadeIn in{c->idx.p, c->sv.p, c->col.p};
-        prof_mark(c, st, "k_tile");
-        if (depth_mode) k_tile<true><<<ntiles, 256, 0, st>>>(fp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, color32, depth_dev);
-        else            k_tile<false><<<ntiles, 256, 0, st>>>(fp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, color32, depth_dev);
-        c->launches++;
+        for (int b = 0; b < nb; ++b) {
+            BatchParams& bp = batches[b];
+            const int n = bp.hi - bp.lo;
+            while (n > 0 && ((n - 1) >> bp.chunk_shift) >= NCHUNK) bp.chunk_shift++;
+            if (n > 0) {
+                prof_mark(c, st, "k_setup");
+                if (depth_mode) k_setup<true><<<div_up(n, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
+                else            k_setup<false><<<div_up(n, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
+                c->launches++;
+            }
+            const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
+            c->epoch++;
+            prof_mark(c, st, "k_scan");
+            k_scan<<<nblocks, SCAN_THREADS, 0, st>>>(c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, fp, bp.index, d_status);
+            c->ticket_base += nblocks;
+            c->launches++;
+            if (n > 0) {
+                prof_mark(c, st, "k_bin_fill");
+                const unsigned grid = std::min<unsigned>(div_up(n, 256), 148 * 8);
+                k_bin_fill<<<grid, 256, 0, st>>>(c->recs.p, d_status, fp, bp, c->cursor.p, c->pairs.p, c->tile_done.p);
+                c->launches++;
+            }
+            prof_mark(c, st, "k_tile");
+            if (depth_mode) k_tile<true><<<fp.ntiles, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            else            k_tile<false><<<fp.ntiles, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            c->launches++;
+        }
     } else {
         if (prim == SR_VERTICES) {
             const int ncorners = (int)((c->nidx / 3) * 3);
@@ -256,7 +281,9 @@ int collect_status(sr_ctx* c, size_t nviews, cudaStream_t st, std::vector<size_t
     unsigned need = 0;
     for (size_t i = 0; i < nviews; ++i) {
         const ViewStatus& s = c->h_status[i];
-        if (s.total_pairs > c->pairs.cap) { rerun->push_back(i); need = std::max(need, s.total_pairs); }
+        unsigned most = 0;
+        for (int b = 0; b < MAX_BATCHES; ++b) most = std::max(most, s.total_pairs[b]);
+        if (most > c->pairs.cap) { rerun->push_back(i); need = std::max(need, most); }
     }
     if (!rerun->empty()) {
         size_t want = (size_t)need + need / 4 + 1024;
@@ -274,8 +301,17 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
         c->stats.primitives += c->nidx / per;
         c->stats.domain_skipped += s.domain_skipped;
         c->stats.small_tris += s.n_small;
-        c->stats.binned_tris += s.n_large;
-        c->stats.tile_pairs += s.total_pairs;
+        for (int b = 0; b < MAX_BATCHES; ++b) { c->stats.binned_tris += s.n_large[b]; c->stats.tile_pairs += s.total_pairs[b]; }
+        c->stats.pairs_consumed += s.pairs_consumed;
+        c->stats.batches_run += s.batches_run;
+    }
+    // adaptive policy for the next call (results are identical either way): batch when most list entries of a
+    // single-batch frame were never read; go back when batching did not retire the frame early
+    if (prim == SR_TRIANGLE && nviews > 0) {
+        const ViewStatus& s = c->h_status[nviews - 1];
+        if (c->force_batches >= 0) c->batched_mode = c->force_batches != 0;
+        else if (!c->batched_mode) c->batched_mode = s.total_pairs[0] >= (1u << 18) && s.pairs_consumed * 2 < s.total_pairs[0];
+        else if (s.batches_run >= 5) c->batched_mode = false;
     }
 }
 
@@ -336,6 +372,7 @@ int sr_create(sr_ctx** out, int device) {
     if (cudaSetDevice(device) != cudaSuccess) return SR_ERR_CUDA;
     sr_ctx* c = new sr_ctx();
     c->device = device;
+    if (const char* e = getenv("SR_BATCHES")) { c->force_batches = atoi(e); c->batched_mode = c->force_batches > 0; }
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < 2; ++i)
@@ -355,7 +392,7 @@ void sr_destroy(sr_ctx* c) {
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release();
     c->counts.release(); c->cursor.release(); c->pairs.release(); c->vis32.release(); c->vis64.release();
-    c->look.release(); c->ticket.release(); c->status.release();
+    c->look.release(); c->ticket.release(); c->status.release(); c->tile_done.release();
     for (int i = 0; i < 2; ++i) {
         c->out_color[i].release(); c->out_depth[i].release();
         if (c->ev_render[i]) cudaEventDestroy(c->ev_render[i]);
@@ -535,7 +572,12 @@ int sr_set_profiling(sr_ctx* c, int enabled) {
 int sr_get_kernel_times(sr_ctx* c, const char** names, float* ms, int cap) {
     if (!c || !names || !ms) return 0;
     int n = 0;
-    for (int i = 0; i + 1 < c->prof_n && n < cap; ++i, ++n) { names[n] = c->prof_name[i]; ms[n] = c->prof_ms[i]; }
+    for (int i = 0; i + 1 < c->prof_n; ++i) {          // batches repeat kernels: sum by name
+        int k = 0;
+        while (k < n && std::strcmp(names[k], c->prof_name[i]) != 0) ++k;
+        if (k == n) { if (n >= cap) continue; names[n] = c->prof_name[i]; ms[n] = 0.0f; ++n; }
+        ms[k] += c->prof_ms[i];
+    }
     return n;
 }
 

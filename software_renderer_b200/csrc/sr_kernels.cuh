@@ -17,7 +17,8 @@ namespace sr {
 
 constexpr int TILE = 16;             // tile edge in pixels
 constexpr int TILE_SHIFT = 4;
-constexpr int NCHUNK = 64;           // index chunks per tile list (early-out granularity)
+constexpr int NCHUNK = 16;           // index chunks per tile list and batch (early-out granularity)
+constexpr int MAX_BATCHES = 8;       // index-descending batches per frame (depth off, heavy overdraw)
 constexpr int SMALL_MAX = 8;         // direct path: clipped bbox at most SMALL_MAX x SMALL_MAX pixels
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;        // per thread -> 2048 counters per CTA
@@ -25,10 +26,14 @@ constexpr int TILE_BATCH = 16;       // triangles per coverage batch in k_tile
 
 // Per-view counters, read back by the host after the frame.
 struct ViewStatus {
-    unsigned n_large;        // triangles appended to the bin list
-    unsigned n_small;        // triangles rasterized directly
-    unsigned domain_skipped; // primitives (or .vertices corners) outside the valid domain
-    unsigned total_pairs;    // (triangle, tile) pairs requested (may exceed capacity -> frame is re-run)
+    unsigned n_large[MAX_BATCHES];      // triangles appended to the bin list, per batch
+    unsigned total_pairs[MAX_BATCHES];  // (triangle, tile) pairs requested per batch (> capacity -> frame is re-run)
+    unsigned n_small;                   // triangles rasterized directly
+    unsigned domain_skipped;            // primitives (or .vertices corners) outside the valid domain
+    unsigned tiles_done;                // tiles shaded before the final batch (batched mode)
+    unsigned batches_run;               // batches that still had unfinished tiles when they started
+    unsigned long long pairs_consumed;  // pairs the tile kernel actually processed (early-out feedback)
+    unsigned long long _pad;
 };
 
 // Bin-list record of a large triangle: truncated corners in ORIGINAL order (R:251), sort permutation (R:271).
@@ -84,67 +89,91 @@ __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ pos
     sv[i] = make_float4(s.x, s.y, s.z, 0.0f);
 }
 
+
 // ---------------------------------------------------------------------------------------------------------------
-// K2: triangle setup, direct raster of small triangles, bin-list append + (tile, chunk) counting of large ones.
+// Frame / batch parameters.
+// With the depth test off, visibility is "highest primitive index wins" (R:222-229 + R:268).  A frame can then be
+// processed in index-DESCENDING batches: once every pixel of a tile has been covered by a batch, no triangle of a
+// later (lower-index) batch can change it, so the tile is shaded and retired (tile_done[tile] = frame epoch) and
+// later batches neither bin nor rasterize into it.  The image is identical to the sequential loop's.
 // ---------------------------------------------------------------------------------------------------------------
 struct FrameParams {
     int width, height;
-    int tiles_x, tiles_y;
-    int ntris;
-    int chunk_shift;          // chunk = prim >> chunk_shift  (< NCHUNK)
+    int tiles_x, tiles_y, ntiles;
     unsigned pair_capacity;
+    unsigned epoch;           // frame stamp for tile_done[]
+    int batched;              // 1: several index-descending batches (depth off only)
+};
+struct BatchParams {
+    int lo, hi;               // primitive range [lo, hi) of this batch
+    int chunk_shift;          // chunk = (prim - lo) >> chunk_shift  (< NCHUNK)
+    int index;                // batch ordinal
+    int final_batch;          // 1: every tile still open is shaded at the end of this batch
 };
 
-template <bool DEPTH>
-__device__ __forceinline__ void raster_direct(const SortedTri& s, int ax, int ay, int bx, int by, int cx, int cy,
-                                              float za, float zb, float zc, unsigned prim, int y0, int y1, int W,
-                                              unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64) {
-    BaryT bt;
-    if (DEPTH) bt = bary_setup(ax, ay, bx, by, cx, cy);
-    for (int y = y0; y <= y1; ++y) {
-        int l, r;
-        span_row(s, y, l, r);
-        l = max(l, 0);
-        r = min(r, W - 1);
-        for (int x = l; x <= r; ++x) {
-            size_t o = (size_t)y * W + x;
-            if (DEPTH) {
-                float3 w = bary_weights(bt, x, y);
-                float d = blend3(za, zb, zc, w);
-                if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, prim));
-            } else {
-                atomicMax(vis32 + o, prim + 1u);
-            }
+// Spreads `n` items per lane evenly over the warp: calls f(src_lane, item) once per item.  Source-lane data must
+// be read from shared memory (f runs divergently).
+template <class F>
+__device__ __forceinline__ void warp_balance(int n, F&& f) {
+    const unsigned lane = threadIdx.x & 31;
+    int incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += t; }
+    const int excl = incl - n;
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    for (int base = 0; base < total; base += 32) {
+        const int k = base + (int)lane;
+        int j = 0;                                   // largest j with excl[j] <= k
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const int e = __shfl_sync(0xffffffffu, excl, j + step);
+            if (e <= k) j += step;
         }
+        const int ej = __shfl_sync(0xffffffffu, excl, j);
+        if (k < total) f(j, k - ej);
     }
 }
 
+struct __align__(16) StagedTri { int x0, y0, x1, y1, x2, y2; unsigned prim; int ystart; };   // sorted corners
+struct __align__(16) StagedRect { int tx0, ty0, w, slot; };                                   // tile rectangle; w | cslot<<16
+
+// ---------------------------------------------------------------------------------------------------------------
+// K2: triangle setup (R:238-243, R:271-273), direct raster of small triangles, bin-list append and per-(tile, chunk)
+// counting of large ones.  Both inner loops (rows of small triangles, tiles of large ones) are re-balanced over
+// the warp, so one big triangle does not serialize 31 idle lanes.
+// ---------------------------------------------------------------------------------------------------------------
 template <bool DEPTH>
 __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, const float4* __restrict__ sv, FrameParams fp,
-                                               unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
-                                               TriRec* __restrict__ recs, unsigned* __restrict__ counts,
+                                               BatchParams bp, unsigned* __restrict__ vis32,
+                                               unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
+                                               unsigned* __restrict__ counts, const unsigned* __restrict__ tile_done,
                                                ViewStatus* __restrict__ status) {
-    const int prim = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ StagedTri s_tri[256];
+    __shared__ StagedRect s_rect[256];
+    __shared__ BaryT s_bt[DEPTH ? 256 : 1];
+    __shared__ float s_z[DEPTH ? 256 : 1][3];
+
+    if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
+    if (fp.batched && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&status->batches_run, 1u);
+
+    const int prim = bp.lo + blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
-    bool valid = prim < fp.ntris;
+    const bool valid = prim < bp.hi;
     bool skipped = false, small = false, large = false;
     SortedTri s = {};
     int ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, y0 = 0, y1 = -1, xmin = 0, xmax = -1;
-    float za = 0, zb = 0, zc = 0;
     unsigned perm = 0;
     if (valid) {
         const int i0 = idx[3 * (size_t)prim], i1 = idx[3 * (size_t)prim + 1], i2 = idx[3 * (size_t)prim + 2];
         const float4 a = sv[i0], b = sv[i1], c = sv[i2];
         if (!(in_domain(a.x) && in_domain(a.y) && in_domain(b.x) && in_domain(b.y) && in_domain(c.x) && in_domain(c.y))) {
-            skipped = true;
+            skipped = true;                                         // the reference traps here (R:251, R:271)
         } else {
             perm = sort3_perm(a.y, b.y, c.y);                       // R:271 float keys, strict <, stable
             ax = __float2int_rz(a.x); ay = __float2int_rz(a.y);     // simd_long2(...) truncates toward zero
             bx = __float2int_rz(b.x); by = __float2int_rz(b.y);
             cx = __float2int_rz(c.x); cy = __float2int_rz(c.y);
-            za = a.z; zb = b.z; zc = c.z;
-            TriRec t = {ax, ay, bx, by, cx, cy, (unsigned)prim, perm};
-            s = sorted_of(t);
+            s = sorted_of(TriRec{ax, ay, bx, by, cx, cy, (unsigned)prim, perm});
             // result-preserving clip/cull: off-screen pixels are rejected one by one by R:246-250
             y0 = max(s.y0, 0);
             y1 = min(s.y2, fp.height - 1);
@@ -154,6 +183,20 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
                 small = (y1 - y0 < SMALL_MAX) && (xmax - xmin < SMALL_MAX);
                 large = !small;
             }
+            if (DEPTH && small) {
+                s_bt[threadIdx.x] = bary_setup(ax, ay, bx, by, cx, cy);
+                s_z[threadIdx.x][0] = a.z; s_z[threadIdx.x][1] = b.z; s_z[threadIdx.x][2] = c.z;
+            }
+        }
+    }
+    int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
+    if (fp.batched && (small || large)) {
+        // retire triangles whose tiles are all done (cheap test for footprints of at most 2x2 tiles)
+        if (tx1 - tx0 <= 1 && ty1 - ty0 <= 1) {
+            bool open = false;
+            for (int ty = ty0; ty <= ty1; ++ty)
+                for (int tx = tx0; tx <= tx1; ++tx) open |= tile_done[ty * fp.tiles_x + tx] != fp.epoch;
+            if (!open) small = large = false;
         }
     }
     // warp-aggregated counters and bin-list append
@@ -164,104 +207,164 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     if (lane == 0) {
         if (m_skip) atomicAdd(&status->domain_skipped, __popc(m_skip));
         if (m_small) atomicAdd(&status->n_small, __popc(m_small));
-        if (m_large) base = atomicAdd(&status->n_large, __popc(m_large));
+        if (m_large) base = atomicAdd(&status->n_large[bp.index], __popc(m_large));
     }
     base = __shfl_sync(0xffffffffu, base, 0);
+    unsigned slot = 0;
     if (large) {
-        const unsigned slot = base + __popc(m_large & ((1u << lane) - 1u));
+        slot = base + __popc(m_large & ((1u << lane) - 1u));
         recs[slot] = TriRec{ax, ay, bx, by, cx, cy, (unsigned)prim, perm};
-        // count per (tile, chunk); chunks are stored in DESCENDING index order inside each tile list
-        const int cslot = NCHUNK - 1 - (prim >> fp.chunk_shift);
-        const int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
-        for (int ty = ty0; ty <= ty1; ++ty)
-            for (int tx = tx0; tx <= tx1; ++tx)
-                atomicAdd(&counts[(size_t)(ty * fp.tiles_x + tx) * NCHUNK + cslot], 1u);
     }
-    if (small) raster_direct<DEPTH>(s, ax, ay, bx, by, cx, cy, za, zb, zc, (unsigned)prim, y0, y1, fp.width, vis32, vis64);
+    s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0};
+    // chunks are stored in DESCENDING index order inside each tile list
+    const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
+    s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
+    __syncwarp();
+    const int wbase = threadIdx.x & ~31;
+
+    // (a) large triangles: one item per bbox tile -> counts[tile][chunk]++
+    warp_balance(large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0, [&](int src, int item) {
+        const StagedRect r = s_rect[wbase + src];
+        const int w = r.w & 0xffff, cs = r.w >> 16;
+        const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
+        const int tile = ty * fp.tiles_x + tx;
+        if (fp.batched && tile_done[tile] == fp.epoch) return;
+        atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
+    });
+
+    // (b) small triangles: one item per clipped row -> global atomics on the visibility words
+    warp_balance(small ? (y1 - y0 + 1) : 0, [&](int src, int item) {
+        const StagedTri t = s_tri[wbase + src];
+        const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
+        const int y = t.ystart + item;
+        int l, r;
+        span_row(st, y, l, r);                               // R:276-280
+        l = max(l, 0);
+        r = min(r, fp.width - 1);
+        for (int x = l; x <= r; ++x) {                       // R:281
+            if (fp.batched && tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] == fp.epoch) continue;
+            const size_t o = (size_t)y * fp.width + x;
+            if (DEPTH) {
+                const float3 w = bary_weights(s_bt[wbase + src], x, y);
+                const float d = blend3(s_z[wbase + src][0], s_z[wbase + src][1], s_z[wbase + src][2], w);
+                if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, t.prim));
+            } else {
+                atomicMax(vis32 + o, t.prim + 1u);
+            }
+        }
+    });
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 // K3: exclusive scan of the (tile, chunk) counters, single pass with decoupled look-back.
-// Writes cursor[i] = exclusive prefix, zeroes counts[i] for the next frame, total -> status->total_pairs.
-// Flags carry the launch epoch so the status array never needs clearing.
+// Writes cursor[i] = exclusive prefix, zeroes counts[i] for the next batch/frame, total -> status->total_pairs[b].
+// Flags carry the launch epoch so the look-back array never needs clearing.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan(unsigned* __restrict__ counts, unsigned* __restrict__ cursor, int n,
                                                        volatile unsigned long long* __restrict__ look, unsigned* __restrict__ ticket,
-                                                       unsigned ticket_base, unsigned epoch, ViewStatus* __restrict__ status) {
+                                                       unsigned ticket_base, unsigned epoch, FrameParams fp, int batch,
+                                                       ViewStatus* __restrict__ status) {
     __shared__ unsigned s_bid, s_prefix, s_warp[SCAN_THREADS / 32];
     if (threadIdx.x == 0) s_bid = atomicAdd(ticket, 1u) - ticket_base;
+    if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;     // nothing was counted
     __syncthreads();
     const unsigned bid = s_bid;
     const int base = (int)bid * SCAN_THREADS * SCAN_ITEMS + threadIdx.x * SCAN_ITEMS;
     unsigned v[SCAN_ITEMS], sum = 0;
+    if (base + SCAN_ITEMS <= n) {
+        const uint4 a = *reinterpret_cast<const uint4*>(counts + base), b = *reinterpret_cast<const uint4*>(counts + base + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        *reinterpret_cast<uint4*>(counts + base) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(counts + base + 4) = make_uint4(0, 0, 0, 0);
+    } else {
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) {
-        v[k] = (base + k < n) ? counts[base + k] : 0u;
-        sum += v[k];
+        for (int k = 0; k < SCAN_ITEMS; ++k) {
+            v[k] = (base + k < n) ? counts[base + k] : 0u;
+            if (base + k < n) counts[base + k] = 0u;
+        }
     }
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) if (base + k < n) counts[base + k] = 0u;
+    for (int k = 0; k < SCAN_ITEMS; ++k) sum += v[k];
     // block exclusive scan of `sum`
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     unsigned inc = sum;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    for (int d = 1; d < 32; d <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= (unsigned)d) inc += t; }
     if (lane == 31) s_warp[wid] = inc;
     __syncthreads();
     if (wid == 0) {
         unsigned w = lane < SCAN_THREADS / 32 ? s_warp[lane] : 0u, winc = w;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, winc, d); if (lane >= d) winc += t; }
+        for (int d = 1; d < 32; d <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, winc, d); if (lane >= (unsigned)d) winc += t; }
         if (lane < SCAN_THREADS / 32) s_warp[lane] = winc - w;   // exclusive warp offsets
         if (lane == SCAN_THREADS / 32 - 1) {
             const unsigned total = winc;
-            // publish aggregate, then look back
-            const unsigned long long F_AGG = (unsigned long long)(2u * epoch + 1u) << 32, F_INC = (unsigned long long)(2u * epoch + 2u) << 32;
+            const unsigned f_agg = 2u * epoch + 1u, f_inc = 2u * epoch + 2u;
             unsigned prefix = 0;
             if (bid == 0) {
-                look[0] = F_INC | total;
+                look[0] = ((unsigned long long)f_inc << 32) | total;
             } else {
-                look[bid] = F_AGG | total;
-                __threadfence();
+                look[bid] = ((unsigned long long)f_agg << 32) | total;
                 for (int j = (int)bid - 1; j >= 0; --j) {
                     unsigned long long f;
-                    do { f = look[j]; } while ((unsigned)(f >> 32) < 2u * epoch + 1u);
+                    do { f = look[j]; } while ((unsigned)(f >> 32) < f_agg);
                     prefix += (unsigned)f;
-                    if ((unsigned)(f >> 32) == 2u * epoch + 2u) break;
+                    if ((unsigned)(f >> 32) == f_inc) break;
                 }
-                look[bid] = F_INC | (unsigned long long)(prefix + total);
+                look[bid] = ((unsigned long long)f_inc << 32) | (unsigned long long)(prefix + total);
             }
             s_prefix = prefix;
-            if ((int)((bid + 1) * SCAN_THREADS * SCAN_ITEMS) >= n) status->total_pairs = prefix + total;
+            if ((int)((bid + 1) * SCAN_THREADS * SCAN_ITEMS) >= n) status->total_pairs[batch] = prefix + total;
         }
     }
     __syncthreads();
     unsigned run = s_prefix + s_warp[wid] + (inc - sum);
+    unsigned o[SCAN_ITEMS];
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) {
-        if (base + k < n) cursor[base + k] = run;
-        run += v[k];
+    for (int k = 0; k < SCAN_ITEMS; ++k) { o[k] = run; run += v[k]; }
+    if (base + SCAN_ITEMS <= n) {
+        *reinterpret_cast<uint4*>(cursor + base) = make_uint4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<uint4*>(cursor + base + 4) = make_uint4(o[4], o[5], o[6], o[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k) if (base + k < n) cursor[base + k] = o[k];
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 // K4: fill the per-tile lists.  pairs[pos] = bin-list slot.  After this kernel cursor[i] = END of segment i.
+// One record per lane, the (record, tile) pairs re-balanced over the warp.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ recs, const ViewStatus* __restrict__ status,
-                                                  FrameParams fp, unsigned* __restrict__ cursor, unsigned* __restrict__ pairs) {
-    const unsigned n = status->n_large;
-    for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
-        const TriRec t = recs[slot];
-        const SortedTri s = sorted_of(t);
-        const int y0 = max(s.y0, 0), y1 = min(s.y2, fp.height - 1);
-        const int xmin = max(min(t.ax, min(t.bx, t.cx)), 0), xmax = min(max(t.ax, max(t.bx, t.cx)), fp.width - 1);
-        const int cslot = NCHUNK - 1 - (int)(t.prim >> fp.chunk_shift);
-        const int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
-        for (int ty = ty0; ty <= ty1; ++ty)
-            for (int tx = tx0; tx <= tx1; ++tx) {
-                const unsigned pos = atomicAdd(&cursor[(size_t)(ty * fp.tiles_x + tx) * NCHUNK + cslot], 1u);
-                if (pos < fp.pair_capacity) pairs[pos] = slot;
-            }
+                                                  FrameParams fp, BatchParams bp, unsigned* __restrict__ cursor,
+                                                  unsigned* __restrict__ pairs, const unsigned* __restrict__ tile_done) {
+    __shared__ StagedRect s_rect[256];
+    if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;
+    const unsigned n = status->n_large[bp.index];
+    const int wbase = threadIdx.x & ~31;
+    const unsigned n_round = (n + 31u) & ~31u;          // whole warps stay in the loop (shuffles inside)
+    for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_round; slot += gridDim.x * blockDim.x) {
+        int items = 0;
+        if (slot < n) {
+            const TriRec t = recs[slot];
+            const int y0 = max(min(t.ay, min(t.by, t.cy)), 0), y1 = min(max(t.ay, max(t.by, t.cy)), fp.height - 1);
+            const int xmin = max(min(t.ax, min(t.bx, t.cx)), 0), xmax = min(max(t.ax, max(t.bx, t.cx)), fp.width - 1);
+            const int cslot = NCHUNK - 1 - (((int)t.prim - bp.lo) >> bp.chunk_shift);
+            const int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
+            s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
+            items = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
+        }
+        __syncwarp();
+        warp_balance(items, [&](int src, int item) {
+            const StagedRect r = s_rect[wbase + src];
+            const int w = r.w & 0xffff, cs = r.w >> 16;
+            const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
+            const int tile = ty * fp.tiles_x + tx;
+            if (fp.batched && tile_done[tile] == fp.epoch) return;
+            const unsigned pos = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);
+            if (pos < fp.pair_capacity) pairs[pos] = (unsigned)r.slot;
+        });
+        __syncwarp();
     }
 }
 
@@ -276,6 +379,8 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
 // the tile holds an index no remaining triangle can beat: the image is identical, overdraw work is not done.
 // The kernel also consumes (and re-clears) the global visibility words written by the direct path, shades the
 // winner (R:251-268) and writes colour and depth exactly once per pixel — the clears of R:205-206 are fused here.
+// In batched mode a tile that is not yet fully covered parks its visibility words in global memory for the next
+// batch; a fully covered one is shaded and retired.
 // ---------------------------------------------------------------------------------------------------------------
 struct ShadeIn {
     const int* idx;
@@ -296,9 +401,10 @@ __device__ __forceinline__ void shade_pixel(const ShadeIn& in, unsigned prim, in
 }
 
 template <bool DEPTH>
-__global__ void __launch_bounds__(256) k_tile(FrameParams fp, ShadeIn in, const TriRec* __restrict__ recs,
+__global__ void __launch_bounds__(256) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
                                               const unsigned* __restrict__ cursor, const unsigned* __restrict__ pairs,
                                               unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
+                                              unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status,
                                               unsigned* __restrict__ color_out, float* __restrict__ depth_out) {
     __shared__ __align__(16) unsigned short s_mask[TILE][TILE_BATCH];
     __shared__ unsigned s_prim[TILE_BATCH];
@@ -306,6 +412,7 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, ShadeIn in, const 
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
 
     const int tile = blockIdx.x;
+    if (fp.batched && tile_done[tile] == fp.epoch) return;          // retired by an earlier batch
     const int tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
@@ -321,19 +428,25 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, ShadeIn in, const 
     }
 
     const size_t seg = (size_t)tile * NCHUNK;
-    unsigned p = seg == 0 ? 0u : cursor[seg - 1];
+    const unsigned begin = seg == 0 ? 0u : cursor[seg - 1];
     const unsigned end = min(cursor[seg + NCHUNK - 1], fp.pair_capacity);
+    unsigned p = begin;
     const int x_lo = tx * TILE, x_hi = min(tx * TILE + TILE - 1, fp.width - 1);
+    const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
+    const int yy = ty * TILE + row;
+
+    // software pipeline: the record of the NEXT batch is in flight while the current one is processed
+    TriRec nxt = {};
+    if (p + j < end) nxt = recs[pairs[p + j]];
 
     while (p < end) {
         const int n = min((unsigned)TILE_BATCH, end - p);
+        const TriRec t = nxt;
+        if (p + TILE_BATCH + j < end) nxt = recs[pairs[p + TILE_BATCH + j]];
         {   // phase A: (triangle j, row) -> column mask
-            const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);
             unsigned mask = 0;
             if (j < n) {
-                const TriRec t = recs[pairs[p + j]];
                 const SortedTri s = sorted_of(t);
-                const int yy = ty * TILE + row;
                 if (yy >= s.y0 && yy <= s.y2 && yy < fp.height) {
                     int l, r;
                     span_row(s, yy, l, r);
@@ -358,15 +471,15 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, ShadeIn in, const 
             const uint4 m1 = *reinterpret_cast<const uint4*>(&s_mask[py][8]);
             const unsigned mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
-            for (int j = 0; j < TILE_BATCH; ++j) {
-                const unsigned m = (mw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-                if (j < n && ((m >> px) & 1u)) {
+            for (int jj = 0; jj < TILE_BATCH; ++jj) {
+                const unsigned m = (mw[jj >> 1] >> ((jj & 1) * 16)) & 0xffffu;
+                if (jj < n && ((m >> px) & 1u)) {
                     if (DEPTH) {
-                        const float3 w = bary_weights(s_bt[j], x, y);
-                        const float d = blend3(s_z[j][0], s_z[j][1], s_z[j][2], w);
-                        if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[j]));
+                        const float3 w = bary_weights(s_bt[jj], x, y);
+                        const float d = blend3(s_z[jj][0], s_z[jj][1], s_z[jj][2], w);
+                        if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[jj]));
                     } else {
-                        v = max(v, s_prim[j] + 1u);
+                        v = max(v, s_prim[jj] + 1u);
                     }
                 }
             }
@@ -375,14 +488,22 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, ShadeIn in, const 
         if (DEPTH) {
             __syncthreads();
         } else {
-            // every remaining pair has prim < thr (chunks are stored in descending order)
-            const unsigned thr = ((s_prim[n - 1] >> fp.chunk_shift) + 1u) << fp.chunk_shift;
+            // every remaining pair of this batch has prim < thr (chunks are stored in descending order)
+            const unsigned thr = (unsigned)bp.lo + ((((s_prim[n - 1] - (unsigned)bp.lo) >> bp.chunk_shift) + 1u) << bp.chunk_shift);
             const bool final_px = !inside || v > thr;    // v - 1 >= thr
             if (__syncthreads_and(final_px)) break;
         }
     }
+    if (tid == 0 && p > begin) atomicAdd(&status->pairs_consumed, (unsigned long long)(p - begin));
 
+    bool shade_now = true;
+    if (fp.batched && !bp.final_batch) {
+        // a pixel covered by this or an earlier batch cannot be changed by later (lower-index) batches
+        shade_now = __syncthreads_and(!inside || v != 0u) != 0;
+        if (shade_now && tid == 0) { tile_done[tile] = fp.epoch; atomicAdd(&status->tiles_done, 1u); }
+    }
     if (!inside) return;
+    if (!shade_now) { if (v) vis32[o] = v; return; }     // park for the next batch
     unsigned bgra = 0u;                                  // clear colour (R:205)
     float depth = __int_as_float(0x7f800000);            // +inf (R:206)
     if (DEPTH) { if (k != SR_KEY_EMPTY) shade_pixel(in, (unsigned)k, x, y, true, bgra, depth); }

@@ -46,7 +46,7 @@ class SrStats(ctypes.Structure):
     _fields_ = [
         ("primitives", ctypes.c_uint64), ("domain_skipped", ctypes.c_uint64), ("small_tris", ctypes.c_uint64),
         ("binned_tris", ctypes.c_uint64), ("tile_pairs", ctypes.c_uint64), ("bin_regrows", ctypes.c_uint64),
-        ("gpu_launches", ctypes.c_uint64), ("gpu_ms", ctypes.c_float),
+        ("pairs_consumed", ctypes.c_uint64), ("batches_run", ctypes.c_uint64), ("gpu_launches", ctypes.c_uint64), ("gpu_ms", ctypes.c_float),
     ]
 
     def as_dict(self):
@@ -254,7 +254,7 @@ class CudaRenderer:
         self._lib.sr_set_profiling(self._ctx, 1 if enabled else 0)
 
     def kernel_times(self) -> dict:
-        names = (ctypes.c_char_p * 16)()
-        ms = (ctypes.c_float * 16)()
-        n = self._lib.sr_get_kernel_times(self._ctx, names, ms, 16)
+        names = (ctypes.c_char_p * 32)()
+        ms = (ctypes.c_float * 32)()
+        n = self._lib.sr_get_kernel_times(self._ctx, names, ms, 32)
         return {names[i].decode(): float(ms[i]) for i in range(n)}

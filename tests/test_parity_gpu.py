@@ -219,3 +219,57 @@ def test_repeatability_and_self_clearing(renderer):
     b = [gpu_render(renderer, v, i, S.app_transform(t), 400, 300, depth_test=dt) for t in (0.1, 0.2) for dt in (False, True)]
     for (c1, d1), (c2, d2) in zip(a, b):
         assert np.array_equal(c1, c2) and np.array_equal(d1, d2)
+
+
+@pytest.fixture(scope="module")
+def batched_renderer():
+    """A context forced into index-descending batch mode (SR_BATCHES=1), which the adaptive policy otherwise only
+    picks for heavy-overdraw frames."""
+    import os
+    os.environ["SR_BATCHES"] = "1"
+    try:
+        r = srb.CudaRenderer(0)
+    finally:
+        del os.environ["SR_BATCHES"]
+    yield r
+    r.close()
+
+
+@pytest.mark.parametrize("case", ["soup", "soup_rot", "ico", "big", "sparse", "cube_sphere"])
+def test_batched_mode_is_identical(batched_renderer, case):
+    r = batched_renderer
+    if case == "soup":
+        v, i = S.triangle_soup(200_000, 1280, 720, seed=9)
+        assert_same(r, v, i, S.soup_transform(1), 1280, 720)
+        assert r.stats()["batches_run"] >= 1
+    elif case == "soup_rot":
+        v, i = S.triangle_soup(150_000, 801, 603, seed=10)      # partial tiles + two consecutive frames
+        assert_same(r, v, i, S.soup_transform(0), 801, 603)
+        assert_same(r, v, i, S.soup_transform(40), 801, 603)
+    elif case == "ico":
+        v, i = S.icosphere(6)
+        assert_same(r, v, i, S.app_transform(0.3), 1920, 1080)
+    elif case == "big":
+        v, i = random_tris(61, 70_000, spread=1.2, small=0.3)   # large triangles, every tile retires early
+        assert_same(r, v, i, I4, 640, 480)
+        s = r.stats()
+        assert s["batches_run"] < 5 and s["pairs_consumed"] < s["tile_pairs"]
+    elif case == "sparse":
+        v, i = random_tris(62, 70_000, spread=0.4, small=0.01)  # most of the screen stays background
+        assert_same(r, v, i, I4, 640, 480)
+        assert r.stats()["batches_run"] == 5
+    else:
+        v, i = S.cube_sphere(120)
+        assert_same(r, v, i, S.app_transform(0.7), 1024, 1024)
+
+
+def test_adaptive_policy_switches_and_stays_exact(renderer):
+    v, i = S.triangle_soup(300_000, 1280, 720, seed=12)
+    seen = set()
+    for k in range(4):
+        assert_same(renderer, v, i, S.soup_transform(k), 1280, 720)
+        seen.add(renderer.stats()["batches_run"] > 0)
+    assert seen == {False, True}            # first frame single-batch, later frames batched
+    v, i = S.icosphere(5)
+    for k in range(3):
+        assert_same(renderer, v, i, S.app_transform(0.1 * k), 1280, 720)
