@@ -12,6 +12,7 @@
 //   k_points_*           PrimitiveType.vertices (R:295-302); also the clear-only path of .line (R:289-293)
 #pragma once
 #include "sr_math.cuh"
+#include <cuda_pipeline.h>
 
 namespace sr {
 
@@ -36,22 +37,33 @@ struct ViewStatus {
     unsigned long long _pad;
 };
 
-// Bin-list record of a large triangle: truncated corners in ORIGINAL order (R:251), sort permutation (R:271).
+// Bin-list record of a large triangle (64 B): corners SORTED as R:271 leaves them, the sort permutation (to get
+// back to the original a,b,c order of R:251 for the depth mode), and the three per-edge reciprocals of sr_math.cuh.
 struct __align__(16) TriRec {
-    int ax, ay, bx, by, cx, cy;
+    int x0, y0, x1, y1, x2, y2;
     unsigned prim;
-    unsigned perm;
+    unsigned perm;                       // sorted position k holds original corner (perm >> 2k) & 3
+    unsigned long long m01, m12, m02;    // edge_magic(y1-y0), (y2-y1), (y2-y0)
+    unsigned long long _pad;
 };
 
-__device__ __forceinline__ SortedTri sorted_of(const TriRec& t) {
-    const int xs[3] = {t.ax, t.bx, t.cx};
-    const int ys[3] = {t.ay, t.by, t.cy};
+__device__ __forceinline__ SortedTri sort_corners(int ax, int ay, int bx, int by, int cx, int cy, unsigned perm) {
+    const unsigned i0 = perm & 3, i1 = (perm >> 2) & 3, i2 = (perm >> 4) & 3;
     SortedTri s;
-    const unsigned i0 = t.perm & 3, i1 = (t.perm >> 2) & 3, i2 = (t.perm >> 4) & 3;
-    s.x0 = i0 == 0 ? xs[0] : (i0 == 1 ? xs[1] : xs[2]);  s.y0 = i0 == 0 ? ys[0] : (i0 == 1 ? ys[1] : ys[2]);
-    s.x1 = i1 == 0 ? xs[0] : (i1 == 1 ? xs[1] : xs[2]);  s.y1 = i1 == 0 ? ys[0] : (i1 == 1 ? ys[1] : ys[2]);
-    s.x2 = i2 == 0 ? xs[0] : (i2 == 1 ? xs[1] : xs[2]);  s.y2 = i2 == 0 ? ys[0] : (i2 == 1 ? ys[1] : ys[2]);
+    s.x0 = i0 == 0 ? ax : (i0 == 1 ? bx : cx);  s.y0 = i0 == 0 ? ay : (i0 == 1 ? by : cy);
+    s.x1 = i1 == 0 ? ax : (i1 == 1 ? bx : cx);  s.y1 = i1 == 0 ? ay : (i1 == 1 ? by : cy);
+    s.x2 = i2 == 0 ? ax : (i2 == 1 ? bx : cx);  s.y2 = i2 == 0 ? ay : (i2 == 1 ? by : cy);
     return s;
+}
+// original-order corners (a, b, c) from a record: out[2*orig + {0,1}]
+__device__ __forceinline__ void unsort_corners(const TriRec& t, int out[6]) {
+    const int xs[3] = {t.x0, t.x1, t.x2}, ys[3] = {t.y0, t.y1, t.y2};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const unsigned orig = (t.perm >> (2 * k)) & 3;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) if (orig == (unsigned)q) { out[2 * q] = xs[k]; out[2 * q + 1] = ys[k]; }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -173,7 +185,7 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
             ax = __float2int_rz(a.x); ay = __float2int_rz(a.y);     // simd_long2(...) truncates toward zero
             bx = __float2int_rz(b.x); by = __float2int_rz(b.y);
             cx = __float2int_rz(c.x); cy = __float2int_rz(c.y);
-            s = sorted_of(TriRec{ax, ay, bx, by, cx, cy, (unsigned)prim, perm});
+            s = sort_corners(ax, ay, bx, by, cx, cy, perm);
             // result-preserving clip/cull: off-screen pixels are rejected one by one by R:246-250
             y0 = max(s.y0, 0);
             y1 = min(s.y2, fp.height - 1);
@@ -213,7 +225,8 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     unsigned slot = 0;
     if (large) {
         slot = base + __popc(m_large & ((1u << lane) - 1u));
-        recs[slot] = TriRec{ax, ay, bx, by, cx, cy, (unsigned)prim, perm};
+        recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm,
+                            edge_magic(s.y1 - s.y0), edge_magic(s.y2 - s.y1), edge_magic(s.y2 - s.y0), 0ull};
     }
     s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0};
     // chunks are stored in DESCENDING index order inside each tile list
@@ -347,8 +360,8 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
         int items = 0;
         if (slot < n) {
             const TriRec t = recs[slot];
-            const int y0 = max(min(t.ay, min(t.by, t.cy)), 0), y1 = min(max(t.ay, max(t.by, t.cy)), fp.height - 1);
-            const int xmin = max(min(t.ax, min(t.bx, t.cx)), 0), xmax = min(max(t.ax, max(t.bx, t.cx)), fp.width - 1);
+            const int y0 = max(t.y0, 0), y1 = min(t.y2, fp.height - 1);
+            const int xmin = max(min(t.x0, min(t.x1, t.x2)), 0), xmax = min(max(t.x0, max(t.x1, t.x2)), fp.width - 1);
             const int cslot = NCHUNK - 1 - (((int)t.prim - bp.lo) >> bp.chunk_shift);
             const int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
             s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
@@ -401,13 +414,14 @@ __device__ __forceinline__ void shade_pixel(const ShadeIn& in, unsigned prim, in
 }
 
 template <bool DEPTH>
-__global__ void __launch_bounds__(256) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
+__global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
                                               const unsigned* __restrict__ cursor, const unsigned* __restrict__ pairs,
                                               unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
                                               unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status,
                                               unsigned* __restrict__ color_out, float* __restrict__ depth_out) {
     __shared__ __align__(16) unsigned short s_mask[TILE][TILE_BATCH];
     __shared__ unsigned s_prim[TILE_BATCH];
+    __shared__ TriRec s_rec[2][TILE_BATCH];
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
 
@@ -435,21 +449,34 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, BatchParams bp, Sh
     const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
     const int yy = ty * TILE + row;
 
-    // software pipeline: the record of the NEXT batch is in flight while the current one is processed
-    TriRec nxt = {};
-    if (p + j < end) nxt = recs[pairs[p + j]];
+    // software pipeline: records of the NEXT batch travel global -> shared with cp.async (no registers held) while
+    // the current batch is processed; the slot indices are fetched one batch further ahead.
+    const int part = row;                                  // threads (j, 0..3) copy the four 16-byte quarters of record j
+    auto fetch = [&](int buf, unsigned slot) {
+        if (part < 4) __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][j]) + 16 * part,
+                                              reinterpret_cast<const char*>(recs + slot) + 16 * part, 16);
+    };
+    unsigned slot_next = 0;
+    if (p + j < end && part < 4) fetch(0, pairs[p + j]);
+    __pipeline_commit();
+    if (p + TILE_BATCH + j < end && part < 4) slot_next = pairs[p + TILE_BATCH + j];
+    int cur = 0;
+    __pipeline_wait_prior(0);
+    __syncthreads();                                       // s_rec[0] complete
 
     while (p < end) {
         const int n = min((unsigned)TILE_BATCH, end - p);
-        const TriRec t = nxt;
-        if (p + TILE_BATCH + j < end) nxt = recs[pairs[p + TILE_BATCH + j]];
+        if (p + TILE_BATCH + j < end) fetch(cur ^ 1, slot_next);
+        __pipeline_commit();
+        if (p + 2 * TILE_BATCH + j < end && part < 4) slot_next = pairs[p + 2 * TILE_BATCH + j];
         {   // phase A: (triangle j, row) -> column mask
             unsigned mask = 0;
             if (j < n) {
-                const SortedTri s = sorted_of(t);
+                const TriRec& t = s_rec[cur][j];
+                const SortedTri s = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                 if (yy >= s.y0 && yy <= s.y2 && yy < fp.height) {
                     int l, r;
-                    span_row(s, yy, l, r);
+                    span_row_magic(s, EdgeMagic{t.m01, t.m12, t.m02}, yy, l, r);
                     l = max(l, x_lo);
                     r = min(r, x_hi);
                     if (l <= r) mask = ((2u << (r - l)) - 1u) << (l - x_lo);
@@ -457,7 +484,9 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, BatchParams bp, Sh
                 if (row == 0) {
                     s_prim[j] = t.prim;
                     if (DEPTH) {
-                        s_bt[j] = bary_setup(t.ax, t.ay, t.bx, t.by, t.cx, t.cy);
+                        int oc[6];
+                        unsort_corners(t, oc);
+                        s_bt[j] = bary_setup(oc[0], oc[1], oc[2], oc[3], oc[4], oc[5]);
                         const int i0 = in.idx[3 * (size_t)t.prim], i1 = in.idx[3 * (size_t)t.prim + 1], i2 = in.idx[3 * (size_t)t.prim + 2];
                         s_z[j][0] = in.sv[i0].z; s_z[j][1] = in.sv[i1].z; s_z[j][2] = in.sv[i2].z;
                     }
@@ -485,6 +514,8 @@ __global__ void __launch_bounds__(256) k_tile(FrameParams fp, BatchParams bp, Sh
             }
         }
         p += n;
+        cur ^= 1;
+        __pipeline_wait_prior(0);                          // next records landed (made visible by the barrier below)
         if (DEPTH) {
             __syncthreads();
         } else {

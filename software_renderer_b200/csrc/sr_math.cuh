@@ -53,19 +53,48 @@ __device__ __forceinline__ int lerp_trunc(int sx, int sy, int ex, int ey, int t)
 struct SortedTri { int x0, y0, x1, y1, x2, y2; };   // s0, s1, s2 of R:271 (y0 <= y1 <= y2)
 
 // interpolate(values: leftVertices, t:)  — the 3-point list [s0,s1,s2] (R:272, R:469-475)
+// Rows whose quotient is known without dividing take a shortcut: nt == 0 gives start.x, t >= y2 gives s2.x.
 __device__ __forceinline__ int span_left(const SortedTri& s, int t) {
     if (t >= s.y2) return s.x2;                           // R:470-471 + R:478-480: last row collapses to s2.x
-    if (t >= s.y1) return lerp_trunc(s.x1, s.y1, s.x2, s.y2, t);
-    return lerp_trunc(s.x0, s.y0, s.x1, s.y1, t);
+    if (t >= s.y1) return t == s.y1 ? s.x1 : lerp_trunc(s.x1, s.y1, s.x2, s.y2, t);
+    return t == s.y0 ? s.x0 : lerp_trunc(s.x0, s.y0, s.x1, s.y1, t);
 }
 // interpolate(values: rightVertices, t:) — the 2-point list [s0,s2] (R:273)
 __device__ __forceinline__ int span_right(const SortedTri& s, int t) {
-    if (s.y2 == s.y0) return s.x0;                        // R:486-488
+    if (s.y2 == s.y0 || t == s.y0) return s.x0;           // R:486-488; nt == 0
+    if (t == s.y2) return s.x2;                           // diff*dy/dy is exact
     return lerp_trunc(s.x0, s.y0, s.x2, s.y2, t);
 }
 // One row of R:275-283: returns inclusive [l, r] after the swap of R:278-280.
 __device__ __forceinline__ void span_row(const SortedTri& s, int t, int& l, int& r) {
     int a = span_left(s, t), b = span_right(s, t);
+    l = min(a, b);
+    r = max(a, b);
+}
+
+// ---- the same rule with per-edge reciprocals ---------------------------------------------------------------------
+// For 0 <= n < 2^31 and 1 <= d < 2^31:  floor(n / d) == umul64hi(n << 2, M) with M = floor(2^62 / d) + 1
+// (error term n * (M*d - 2^62) / (d * 2^62) < 1/d, so the floor never moves).  M is computed once per edge in
+// triangle setup; a row then costs one 64-bit multiply-high instead of an integer division.  Larger numerators
+// (far off-screen corners) fall back to the 64-bit division, so the result is always the reference's quotient.
+__device__ __forceinline__ unsigned long long edge_magic(int dy) {
+    return dy > 0 ? (1ull << 62) / (unsigned long long)dy + 1ull : 0ull;
+}
+__device__ __forceinline__ int lerp_magic(int sx, int sy, int ex, int ey, int t, unsigned long long M) {
+    const long long num = ((long long)ex - (long long)sx) * ((long long)t - (long long)sy);
+    const unsigned long long a = (unsigned long long)(num < 0 ? -num : num);
+    unsigned long long q;
+    if (a < (1ull << 31)) q = __umul64hi(a << 2, M);
+    else q = a / (unsigned long long)((long long)ey - (long long)sy);
+    return (int)((long long)sx + (num < 0 ? -(long long)q : (long long)q));
+}
+struct EdgeMagic { unsigned long long m01, m12, m02; };
+__device__ __forceinline__ void span_row_magic(const SortedTri& s, const EdgeMagic& m, int t, int& l, int& r) {
+    int a, b;
+    if (t >= s.y2) a = s.x2;
+    else if (t >= s.y1) a = lerp_magic(s.x1, s.y1, s.x2, s.y2, t, m.m12);
+    else a = lerp_magic(s.x0, s.y0, s.x1, s.y1, t, m.m01);
+    b = (s.y2 == s.y0) ? s.x0 : lerp_magic(s.x0, s.y0, s.x2, s.y2, t, m.m02);
     l = min(a, b);
     r = max(a, b);
 }
