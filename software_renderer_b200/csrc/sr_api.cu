@@ -60,6 +60,7 @@ struct sr_ctx {
     unsigned frame_epoch = 0;
     // adaptive policy (depth off): index-descending batches pay off when most tile-list entries are never read
     bool batched_mode = false;
+    unsigned long long single_batch_pairs = 0;
     int force_batches = -1;                 // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     DevBuf<ViewStatus> status;
     ViewStatus* h_status = nullptr;
@@ -238,8 +239,10 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 c->launches++;
             }
             prof_mark(c, st, "k_tile");
-            if (depth_mode) k_tile<true><<<fp.ntiles, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
-            else            k_tile<false><<<fp.ntiles, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
+            const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;
+            if (depth_mode) k_tile<true><<<tgrid, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            else            k_tile<false><<<tgrid, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
             c->launches++;
         }
     } else {
@@ -310,8 +313,14 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
     if (prim == SR_TRIANGLE && nviews > 0) {
         const ViewStatus& s = c->h_status[nviews - 1];
         if (c->force_batches >= 0) c->batched_mode = c->force_batches != 0;
-        else if (!c->batched_mode) c->batched_mode = s.total_pairs[0] >= (1u << 18) && s.pairs_consumed * 2 < s.total_pairs[0];
-        else if (s.batches_run >= 5) c->batched_mode = false;
+        else if (!c->batched_mode) {
+            c->single_batch_pairs = s.total_pairs[0];
+            c->batched_mode = s.total_pairs[0] >= (1u << 18) && s.pairs_consumed * 2 < s.total_pairs[0];
+        } else {
+            unsigned long long sum = 0;
+            for (int b = 0; b < MAX_BATCHES; ++b) sum += s.total_pairs[b];
+            if (sum * 3 > c->single_batch_pairs) c->batched_mode = false;      // batching no longer saves binning work
+        }
     }
 }
 
@@ -449,6 +458,8 @@ int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64
     c->nverts = nverts;
     c->nidx = nidx;
     c->has_mesh = true;
+    c->batched_mode = c->force_batches > 0;      // the adaptive policy starts over with every mesh
+    c->single_batch_pairs = 0;
     return rc;
 }
 

@@ -310,22 +310,33 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan(unsigned* __restrict__ co
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, winc, d); if (lane >= (unsigned)d) winc += t; }
         if (lane < SCAN_THREADS / 32) s_warp[lane] = winc - w;   // exclusive warp offsets
-        if (lane == SCAN_THREADS / 32 - 1) {
-            const unsigned total = winc;
-            const unsigned f_agg = 2u * epoch + 1u, f_inc = 2u * epoch + 2u;
-            unsigned prefix = 0;
-            if (bid == 0) {
-                look[0] = ((unsigned long long)f_inc << 32) | total;
-            } else {
-                look[bid] = ((unsigned long long)f_agg << 32) | total;
-                for (int j = (int)bid - 1; j >= 0; --j) {
+        const unsigned total = __shfl_sync(0xffffffffu, winc, SCAN_THREADS / 32 - 1);
+        const unsigned f_agg = 2u * epoch + 1u, f_inc = 2u * epoch + 2u;
+        unsigned prefix = 0;
+        if (bid == 0) {
+            if (lane == 0) look[0] = ((unsigned long long)f_inc << 32) | total;
+        } else {
+            if (lane == 0) look[bid] = ((unsigned long long)f_agg << 32) | total;
+            // warp-wide look-back: lane l inspects predecessor bid-1-l (32 predecessors per step)
+            for (int j = (int)bid - 1 - (int)lane;; j -= 32) {
+                unsigned flag = f_inc, val = 0;
+                if (j >= 0) {
                     unsigned long long f;
                     do { f = look[j]; } while ((unsigned)(f >> 32) < f_agg);
-                    prefix += (unsigned)f;
-                    if ((unsigned)(f >> 32) == f_inc) break;
+                    flag = (unsigned)(f >> 32);
+                    val = (unsigned)f;
                 }
-                look[bid] = ((unsigned long long)f_inc << 32) | (unsigned long long)(prefix + total);
+                const unsigned m_inc = __ballot_sync(0xffffffffu, flag == f_inc);
+                const int first = m_inc ? __ffs(m_inc) - 1 : 32;         // nearest predecessor with an inclusive prefix
+                unsigned add = (int)lane <= first ? val : 0u;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) add += __shfl_xor_sync(0xffffffffu, add, d);
+                prefix += add;
+                if (m_inc) break;
             }
+            if (lane == 0) look[bid] = ((unsigned long long)f_inc << 32) | (unsigned long long)(prefix + total);
+        }
+        if (lane == 0) {
             s_prefix = prefix;
             if ((int)((bid + 1) * SCAN_THREADS * SCAN_ITEMS) >= n) status->total_pairs[batch] = prefix + total;
         }
@@ -368,15 +379,40 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
             items = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
         }
         __syncwarp();
-        warp_balance(items, [&](int src, int item) {
-            const StagedRect r = s_rect[wbase + src];
-            const int w = r.w & 0xffff, cs = r.w >> 16;
-            const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
-            const int tile = ty * fp.tiles_x + tx;
-            if (fp.batched && tile_done[tile] == fp.epoch) return;
-            const unsigned pos = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);
-            if (pos < fp.pair_capacity) pairs[pos] = (unsigned)r.slot;
-        });
+        // (record, tile) pairs spread over the warp, four per lane per step so that four list-cursor atomics are in
+        // flight before the first dependent store
+        const unsigned lane = threadIdx.x & 31;
+        int incl = items;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += t; }
+        const int excl = incl - items;
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        for (int base = 0; base < total; base += 128) {
+            unsigned pos[4], val[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = base + u * 32 + (int)lane;
+                int j = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int e = __shfl_sync(0xffffffffu, excl, j + step);
+                    if (e <= k) j += step;
+                }
+                const int ej = __shfl_sync(0xffffffffu, excl, j);
+                pos[u] = 0xffffffffu;
+                if (k < total) {
+                    const StagedRect r = s_rect[wbase + j];
+                    const int item = k - ej, w = r.w & 0xffff, cs = r.w >> 16;
+                    const int tile = (r.ty0 + item / w) * fp.tiles_x + r.tx0 + item % w;
+                    val[u] = (unsigned)r.slot;
+                    if (!(fp.batched && tile_done[tile] == fp.epoch))
+                        pos[u] = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (pos[u] < fp.pair_capacity) pairs[pos[u]] = val[u];
+        }
         __syncwarp();
     }
 }
@@ -425,11 +461,15 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
 
-    const int tile = blockIdx.x;
-    if (fp.batched && tile_done[tile] == fp.epoch) return;          // retired by an earlier batch
-    const int tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
+    const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
+    if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;
+
+    // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA launches
+    for (int tile = blockIdx.x; tile < fp.ntiles; tile += gridDim.x) {
+    if (fp.batched && tile_done[tile] == fp.epoch) continue;        // retired by an earlier batch
+    const int tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
     const int x = tx * TILE + px, y = ty * TILE + py;
     const bool inside = x < fp.width && y < fp.height;
     const size_t o = (size_t)y * fp.width + x;
@@ -446,20 +486,19 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
     const unsigned end = min(cursor[seg + NCHUNK - 1], fp.pair_capacity);
     unsigned p = begin;
     const int x_lo = tx * TILE, x_hi = min(tx * TILE + TILE - 1, fp.width - 1);
-    const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
     const int yy = ty * TILE + row;
 
     // software pipeline: records of the NEXT batch travel global -> shared with cp.async (no registers held) while
     // the current batch is processed; the slot indices are fetched one batch further ahead.
-    const int part = row;                                  // threads (j, 0..3) copy the four 16-byte quarters of record j
     auto fetch = [&](int buf, unsigned slot) {
-        if (part < 4) __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][j]) + 16 * part,
-                                              reinterpret_cast<const char*>(recs + slot) + 16 * part, 16);
+        if (row < 4) __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][j]) + 16 * row,
+                                             reinterpret_cast<const char*>(recs + slot) + 16 * row, 16);
     };
     unsigned slot_next = 0;
-    if (p + j < end && part < 4) fetch(0, pairs[p + j]);
+    __syncthreads();                                       // previous tile of this CTA is done with shared memory
+    if (p + j < end && row < 4) fetch(0, pairs[p + j]);
     __pipeline_commit();
-    if (p + TILE_BATCH + j < end && part < 4) slot_next = pairs[p + TILE_BATCH + j];
+    if (p + TILE_BATCH + j < end && row < 4) slot_next = pairs[p + TILE_BATCH + j];
     int cur = 0;
     __pipeline_wait_prior(0);
     __syncthreads();                                       // s_rec[0] complete
@@ -468,7 +507,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
         const int n = min((unsigned)TILE_BATCH, end - p);
         if (p + TILE_BATCH + j < end) fetch(cur ^ 1, slot_next);
         __pipeline_commit();
-        if (p + 2 * TILE_BATCH + j < end && part < 4) slot_next = pairs[p + 2 * TILE_BATCH + j];
+        if (p + 2 * TILE_BATCH + j < end && row < 4) slot_next = pairs[p + 2 * TILE_BATCH + j];
         {   // phase A: (triangle j, row) -> column mask
             unsigned mask = 0;
             if (j < n) {
@@ -492,24 +531,27 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
                     }
                 }
             }
-            s_mask[row][j] = (unsigned short)mask;
+            s_mask[row][j] = (unsigned short)mask;         // zero for j >= n
         }
         __syncthreads();
-        {   // phase B: each pixel folds the batch into its visibility register
+        {   // phase B: each pixel gathers "which triangles of the batch cover me" into one word (two triangles per
+            // shift/and: bit k = triangle 2k, bit 16+k = triangle 2k+1), then folds only the set bits
             const uint4 m0 = *reinterpret_cast<const uint4*>(&s_mask[py][0]);
             const uint4 m1 = *reinterpret_cast<const uint4*>(&s_mask[py][8]);
             const unsigned mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            unsigned bits = 0;
 #pragma unroll
-            for (int jj = 0; jj < TILE_BATCH; ++jj) {
-                const unsigned m = (mw[jj >> 1] >> ((jj & 1) * 16)) & 0xffffu;
-                if (jj < n && ((m >> px) & 1u)) {
-                    if (DEPTH) {
-                        const float3 w = bary_weights(s_bt[jj], x, y);
-                        const float d = blend3(s_z[jj][0], s_z[jj][1], s_z[jj][2], w);
-                        if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[jj]));
-                    } else {
-                        v = max(v, s_prim[jj] + 1u);
-                    }
+            for (int q = 0; q < 8; ++q) bits |= ((mw[q] >> px) & 0x00010001u) << q;
+            while (bits) {
+                const int b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const int jj = ((b & 15) << 1) | (b >> 4);
+                if (DEPTH) {
+                    const float3 w = bary_weights(s_bt[jj], x, y);
+                    const float d = blend3(s_z[jj][0], s_z[jj][1], s_z[jj][2], w);
+                    if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[jj]));
+                } else {
+                    v = max(v, s_prim[jj] + 1u);
                 }
             }
         }
@@ -525,6 +567,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
             if (__syncthreads_and(final_px)) break;
         }
     }
+    __pipeline_wait_prior(0);
     if (tid == 0 && p > begin) atomicAdd(&status->pairs_consumed, (unsigned long long)(p - begin));
 
     bool shade_now = true;
@@ -533,14 +576,15 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
         shade_now = __syncthreads_and(!inside || v != 0u) != 0;
         if (shade_now && tid == 0) { tile_done[tile] = fp.epoch; atomicAdd(&status->tiles_done, 1u); }
     }
-    if (!inside) return;
-    if (!shade_now) { if (v) vis32[o] = v; return; }     // park for the next batch
+    if (!inside) continue;
+    if (!shade_now) { if (v) vis32[o] = v; continue; }   // park for the next batch
     unsigned bgra = 0u;                                  // clear colour (R:205)
     float depth = __int_as_float(0x7f800000);            // +inf (R:206)
     if (DEPTH) { if (k != SR_KEY_EMPTY) shade_pixel(in, (unsigned)k, x, y, true, bgra, depth); }
     else       { if (v) shade_pixel(in, v - 1u, x, y, false, bgra, depth); }
     color_out[o] = bgra;
     if (depth_out) depth_out[o] = depth;
+    }   // tile loop
 }
 
 // ---------------------------------------------------------------------------------------------------------------
