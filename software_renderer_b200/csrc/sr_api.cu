@@ -61,7 +61,8 @@ struct sr_ctx {
     // adaptive policy (depth off): index-descending batches pay off when most tile-list entries are never read
     bool batched_mode = false;
     unsigned long long single_batch_pairs = 0;
-    int force_batches = -1;                 // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
+    int force_batches = -1;
+    bool use_pdl = true;                 // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     DevBuf<ViewStatus> status;
     ViewStatus* h_status = nullptr;
     size_t h_status_cap = 0;
@@ -120,6 +121,25 @@ void prof_mark(sr_ctx* c, cudaStream_t st, const char* name_of_next) {
     cudaEventRecord(c->prof_ev[c->prof_n], st);
     c->prof_name[c->prof_n] = name_of_next;
     c->prof_n++;
+}
+
+
+// Every frame kernel is launched with programmatic stream serialization (PDL): its CTAs may be scheduled while the
+// previous kernel drains, and block in griddepcontrol.wait (pdl_wait() at the top of each kernel) until that kernel
+// has completed and flushed.  This hides launch latency between the many short kernels of a frame.  SR_PDL=0 disables.
+template <class... KArgs, class... Args>
+void launch_pdl(sr_ctx* c, void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = c->use_pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 int primitive_vertices(int prim) { return prim == SR_LINE ? 2 : 3; }   // R:179-188
@@ -193,7 +213,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
 
     if (prim != SR_LINE && nverts > 0) {
         prof_mark(c, st, "k_transform");
-        k_transform<<<div_up(nverts, 256), 256, 0, st>>>(c->pos.p, nverts, M, (float)W, (float)H, c->sv.p);
+        launch_pdl(c, k_transform, div_up(nverts, 256), 256, st, c->pos.p, nverts, M, (float)W, (float)H, c->sv.p);
         c->launches++;
     }
     if (prim == SR_TRIANGLE) {
@@ -206,12 +226,13 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.epoch = ++c->frame_epoch;
         fp.batched = (!depth_mode && c->batched_mode && ntris >= (1 << 16)) ? 1 : 0;
         const int ncnt = fp.ntiles * NCHUNK;
-        // index-descending batches: T/16, T/16, T/8, T/4, T/2 from the top; one batch otherwise
+        // index-descending batches from the top: T/8, T/8, 3T/4 (the last one usually finds every tile retired);
+        // one batch otherwise
         BatchParams batches[MAX_BATCHES];
         int nb = 0;
         if (fp.batched) {
-            const int cuts[6] = {ntris, ntris - ntris / 16, ntris - ntris / 8, ntris - ntris / 4, ntris / 2, 0};
-            for (int b = 0; b < 5; ++b) batches[nb++] = BatchParams{cuts[b + 1], cuts[b], 0, b, b == 4};
+            const int cuts[4] = {ntris, ntris - ntris / 8, ntris - ntris / 4, 0};
+            for (int b = 0; b < 3; ++b) batches[nb++] = BatchParams{cuts[b + 1], cuts[b], 0, b, b == 2};
         } else {
             batches[nb++] = BatchParams{0, ntris, 0, 0, 1};
         }
@@ -222,27 +243,27 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             while (n > 0 && ((n - 1) >> bp.chunk_shift) >= NCHUNK) bp.chunk_shift++;
             if (n > 0) {
                 prof_mark(c, st, "k_setup");
-                if (depth_mode) k_setup<true><<<div_up(n, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
-                else            k_setup<false><<<div_up(n, 256), 256, 0, st>>>(c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
+                if (depth_mode) launch_pdl(c, k_setup<true>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
+                else            launch_pdl(c, k_setup<false>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
             c->epoch++;
             prof_mark(c, st, "k_scan");
-            k_scan<<<nblocks, SCAN_THREADS, 0, st>>>(c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, fp, bp.index, d_status);
+            launch_pdl(c, k_scan, nblocks, SCAN_THREADS, st, c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, fp, bp.index, d_status);
             c->ticket_base += nblocks;
             c->launches++;
             if (n > 0) {
                 prof_mark(c, st, "k_bin_fill");
                 const unsigned grid = std::min<unsigned>(div_up(n, 256), 148 * 8);
-                k_bin_fill<<<grid, 256, 0, st>>>(c->recs.p, d_status, fp, bp, c->cursor.p, c->pairs.p, c->tile_done.p);
+                launch_pdl(c, k_bin_fill, grid, 256, st, c->recs.p, d_status, fp, bp, c->cursor.p, c->pairs.p, c->tile_done.p);
                 c->launches++;
             }
             prof_mark(c, st, "k_tile");
             // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
             const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;
-            if (depth_mode) k_tile<true><<<tgrid, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
-            else            k_tile<false><<<tgrid, 256, 0, st>>>(fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            if (depth_mode) launch_pdl(c, k_tile<true>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            else            launch_pdl(c, k_tile<false>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
             c->launches++;
         }
     } else {
@@ -250,12 +271,12 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             const int ncorners = (int)((c->nidx / 3) * 3);
             if (ncorners > 0) {
                 prof_mark(c, st, "k_points_scatter");
-                k_points_scatter<<<div_up(ncorners, 256), 256, 0, st>>>(c->idx.p, c->sv.p, ncorners, W, H, c->vis32.p, d_status);
+                launch_pdl(c, k_points_scatter, div_up(ncorners, 256), 256, st, c->idx.p, c->sv.p, ncorners, W, H, c->vis32.p, d_status);
                 c->launches++;
             }
         }
         prof_mark(c, st, "k_points_resolve");
-        k_points_resolve<<<div_up(npx, 256), 256, 0, st>>>(c->idx.p, c->col.p, npx, c->vis32.p, color32, depth_dev);
+        launch_pdl(c, k_points_resolve, div_up(npx, 256), 256, st, c->idx.p, c->col.p, npx, c->vis32.p, color32, depth_dev);
         c->launches++;
     }
     prof_mark(c, st, nullptr);
@@ -381,6 +402,7 @@ int sr_create(sr_ctx** out, int device) {
     if (cudaSetDevice(device) != cudaSuccess) return SR_ERR_CUDA;
     sr_ctx* c = new sr_ctx();
     c->device = device;
+    if (const char* e = getenv("SR_PDL")) c->use_pdl = atoi(e) != 0;
     if (const char* e = getenv("SR_BATCHES")) { c->force_batches = atoi(e); c->batched_mode = c->force_batches > 0; }
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;

@@ -16,6 +16,13 @@
 
 namespace sr {
 
+// Programmatic dependent launch: wait for the previous kernel of the stream (no-op without the launch attribute),
+// then let the next one start scheduling its CTAs behind ours.
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
+}
+
 constexpr int TILE = 16;             // tile edge in pixels
 constexpr int TILE_SHIFT = 4;
 constexpr int NCHUNK = 16;           // index chunks per tile list and batch (early-out granularity)
@@ -94,6 +101,7 @@ __global__ void k_convert_indices(const long long* __restrict__ in, size_t nidx,
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ pos, int nverts, Mat4 M, float fw, float fh,
                                                    float4* __restrict__ sv) {
+    pdl_wait();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nverts) return;
     float x = pos[3 * (size_t)i], y = pos[3 * (size_t)i + 1], z = pos[3 * (size_t)i + 2];
@@ -160,6 +168,7 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, const unsigned* __restrict__ tile_done,
                                                ViewStatus* __restrict__ status) {
+    pdl_wait();
     __shared__ StagedTri s_tri[256];
     __shared__ StagedRect s_rect[256];
     __shared__ BaryT s_bt[DEPTH ? 256 : 1];
@@ -277,6 +286,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan(unsigned* __restrict__ co
                                                        volatile unsigned long long* __restrict__ look, unsigned* __restrict__ ticket,
                                                        unsigned ticket_base, unsigned epoch, FrameParams fp, int batch,
                                                        ViewStatus* __restrict__ status) {
+    pdl_wait();
     __shared__ unsigned s_bid, s_prefix, s_warp[SCAN_THREADS / 32];
     if (threadIdx.x == 0) s_bid = atomicAdd(ticket, 1u) - ticket_base;
     if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;     // nothing was counted
@@ -362,6 +372,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan(unsigned* __restrict__ co
 __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ recs, const ViewStatus* __restrict__ status,
                                                   FrameParams fp, BatchParams bp, unsigned* __restrict__ cursor,
                                                   unsigned* __restrict__ pairs, const unsigned* __restrict__ tile_done) {
+    pdl_wait();
     __shared__ StagedRect s_rect[256];
     if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;
     const unsigned n = status->n_large[bp.index];
@@ -455,6 +466,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
                                               unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
                                               unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status,
                                               unsigned* __restrict__ color_out, float* __restrict__ depth_out) {
+    pdl_wait();
     __shared__ __align__(16) unsigned short s_mask[TILE][TILE_BATCH];
     __shared__ unsigned s_prim[TILE_BATCH];
     __shared__ TriRec s_rec[2][TILE_BATCH];
@@ -593,6 +605,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_points_scatter(const int* __restrict__ idx, const float4* __restrict__ sv, int ncorners,
                                                         int W, int H, unsigned* __restrict__ vis32, ViewStatus* __restrict__ status) {
+    pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     bool skipped = false;
     if (c < ncorners) {
@@ -611,6 +624,7 @@ __global__ void __launch_bounds__(256) k_points_scatter(const int* __restrict__ 
 __global__ void __launch_bounds__(256) k_points_resolve(const int* __restrict__ idx, const float4* __restrict__ col, size_t npx,
                                                         unsigned* __restrict__ vis32, unsigned* __restrict__ color_out,
                                                         float* __restrict__ depth_out) {
+    pdl_wait();
     const size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (o >= npx) return;
     const unsigned v = vis32[o];
