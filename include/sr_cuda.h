@@ -110,7 +110,8 @@ int sr_render_batch(sr_ctx* ctx, const float* transforms_colmajor16, size_t nvie
 
 /* Device-resident variant: outputs are DEVICE pointers (nviews consecutive images), work is enqueued on
  * `cuda_stream` (a cudaStream_t, NULL = the context's own stream) and the call returns without waiting.
- * `transforms_colmajor16` is host memory and is copied before return.  Follow with sr_sync. */
+ * `transforms_colmajor16` is host memory and is copied before return.  Follow with sr_sync.  Consecutive calls with the
+ * same primitive type, size, flags and stream accumulate (no host round trip in between); one sr_sync completes them. */
 int sr_render_device(sr_ctx* ctx, const float* transforms_colmajor16, size_t nviews, int primitive_type,
                      int width, int height, void* color_bgra_dev, void* depth_dev, uint32_t flags,
                      void* cuda_stream);

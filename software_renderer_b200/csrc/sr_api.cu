@@ -80,14 +80,12 @@ struct sr_ctx {
     int prof_n = 0;
     float prof_ms[MAX_PROF] = {};
 
-    // pending asynchronous call (sr_render_device .. sr_sync)
+    // pending asynchronous views (sr_render_device .. sr_sync); several calls may accumulate before one sr_sync
+    struct ViewJob { float m[16]; uint8_t* color; float* depth; };
     struct Pending {
         bool active = false;
-        std::vector<float> transforms;
-        size_t nviews = 0;
+        std::vector<ViewJob> jobs;
         int prim = 0, width = 0, height = 0;
-        uint8_t* color = nullptr;
-        float* depth = nullptr;
         uint32_t flags = 0;
         cudaStream_t stream = nullptr;
     } pending;
@@ -350,21 +348,11 @@ void finish_profile(sr_ctx* c) {
     for (int i = 0; i + 1 < c->prof_n; ++i) cudaEventElapsedTime(&c->prof_ms[i], c->prof_ev[i], c->prof_ev[i + 1]);
 }
 
-// Device-output batch on one stream, including overflow re-runs.  Synchronises.
-int run_device_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, uint8_t* color, float* depth,
-                     uint32_t flags, cudaStream_t st, bool already_enqueued) {
-    const size_t npx = (size_t)W * H;
-    if (!already_enqueued) {
-        int rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
-        if (rc) return rc;
-        SR_CUDA(c, cudaMemsetAsync(c->status.p, 0, nviews * sizeof(ViewStatus), st));
-        SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
-        for (size_t i = 0; i < nviews; ++i) {
-            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, color + 4 * npx * i, depth ? depth + npx * i : nullptr, flags, st, c->status.p + i);
-            if (rc) return rc;
-        }
-        SR_CUDA(c, cudaEventRecord(c->ev_end, st));
-    }
+// Completes the pending device-output views: status read-back, overflow re-runs, stats.  Synchronises `st`.
+int finish_pending(sr_ctx* c) {
+    auto& p = c->pending;
+    const size_t nviews = p.jobs.size();
+    cudaStream_t st = p.stream;
     for (int attempt = 0; attempt < 8; ++attempt) {
         std::vector<size_t> rerun;
         int rc = collect_status(c, nviews, st, &rerun);
@@ -372,7 +360,7 @@ int run_device_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim
         if (rerun.empty()) break;
         for (size_t i : rerun) {
             SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
-            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, color + 4 * npx * i, depth ? depth + npx * i : nullptr, flags, st, c->status.p + i);
+            rc = enqueue_view(c, p.jobs[i].m, p.prim, p.width, p.height, p.jobs[i].color, p.jobs[i].depth, p.flags, st, c->status.p + i);
             if (rc) return rc;
         }
     }
@@ -380,8 +368,9 @@ int run_device_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim
     cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
     c->stats.gpu_ms = ms;
     finish_profile(c);
-    accumulate_stats(c, nviews, prim);
+    accumulate_stats(c, nviews, p.prim);
     c->stats.gpu_launches = c->launches;
+    p.jobs.clear();
     return c->stats.domain_skipped ? SR_ERR_DOMAIN : SR_OK;
 }
 
@@ -445,6 +434,7 @@ int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64
     if ((nverts && !vertices) || (nidx && !indices)) return fail(c, SR_ERR_ARG, "null mesh pointer");
     if (nverts > 0x7FFFFFF0ull || nidx > 3ull * 0x7FFFFFF0ull) return fail(c, SR_ERR_ARG, "mesh too large for 32-bit device indices");
     SR_CUDA(c, cudaSetDevice(c->device));
+    if (c->pending.active) { int prc = sr_sync(c); if (prc == SR_ERR_CUDA) return prc; }
     SR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->has_mesh = false;
     SR_CUDA(c, c->pos.reserve(std::max<size_t>(3 * nverts, 1)));
@@ -491,26 +481,39 @@ int sr_render_device(sr_ctx* c, const float* transforms, size_t nviews, int prim
     if (rc) return rc;
     SR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
-    if (c->pending.active) { rc = sr_sync(c); if (rc == SR_ERR_CUDA) return rc; }
-    c->stats = sr_stats{};
-    c->launches = 0;
-    rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
+    auto& p = c->pending;
+    // calls with the same target format on the same stream accumulate (no host round trip between them)
+    const size_t kStatusViews = 1024;
+    if (p.active && (p.prim != prim || p.width != W || p.height != H || p.flags != flags || p.stream != st ||
+                     p.jobs.size() + nviews > std::max(c->status.cap, kStatusViews))) {
+        rc = sr_sync(c);
+        if (rc == SR_ERR_CUDA) return rc;
+    }
+    const size_t first = p.active ? p.jobs.size() : 0;
+    if (!p.active) {
+        c->stats = sr_stats{};
+        c->launches = 0;
+        p.jobs.clear();
+    }
+    rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, std::max(first + nviews, kStatusViews), st);
     if (rc) return rc;
     const size_t npx = (size_t)W * H;
     uint8_t* color = (uint8_t*)color_dev;
     float* depth = (flags & SR_FLAG_NO_DEPTH_OUT) ? nullptr : (float*)depth_dev;
-    SR_CUDA(c, cudaMemsetAsync(c->status.p, 0, nviews * sizeof(ViewStatus), st));
-    SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+    SR_CUDA(c, cudaMemsetAsync(c->status.p + first, 0, nviews * sizeof(ViewStatus), st));
+    if (!p.active) SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+    p.active = true;
+    p.prim = prim; p.width = W; p.height = H; p.flags = flags; p.stream = st;
     for (size_t i = 0; i < nviews; ++i) {
-        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, color + 4 * npx * i, depth ? depth + npx * i : nullptr, flags, st, c->status.p + i);
+        sr_ctx::ViewJob job;
+        std::memcpy(job.m, transforms + 16 * i, sizeof job.m);
+        job.color = color + 4 * npx * i;
+        job.depth = depth ? depth + npx * i : nullptr;
+        p.jobs.push_back(job);
+        rc = enqueue_view(c, job.m, prim, W, H, job.color, job.depth, flags, st, c->status.p + first + i);
         if (rc) return rc;
     }
     SR_CUDA(c, cudaEventRecord(c->ev_end, st));
-    auto& p = c->pending;
-    p.active = true;
-    p.transforms.assign(transforms, transforms + 16 * nviews);
-    p.nviews = nviews; p.prim = prim; p.width = W; p.height = H;
-    p.color = color; p.depth = depth; p.flags = flags; p.stream = st;
     return SR_OK;
 }
 
@@ -518,9 +521,8 @@ int sr_sync(sr_ctx* c) {
     if (!c) return SR_ERR_ARG;
     if (!c->pending.active) return SR_OK;
     SR_CUDA(c, cudaSetDevice(c->device));
-    auto& p = c->pending;
-    p.active = false;
-    return run_device_batch(c, p.transforms.data(), p.nviews, p.prim, p.width, p.height, p.color, p.depth, p.flags, p.stream, true);
+    c->pending.active = false;
+    return finish_pending(c);
 }
 
 int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, uint8_t* color,
