@@ -303,10 +303,17 @@ def run_cuda(args):
                 traffic = None
         frame_bytes = S.algorithmic_bytes(ntris, nverts, W, H)
         frame_ms = dev_ms / K
-        # CPU baseline: the oracle on one host core (the reference loop is sequential, Renderer.swift:222)
-        stride = 8 if ntris >= 500_000 else 1
-        t_cpu = time_oracle(v, i, xf, W, H, 1, 1, stride)
-        cpu_value = (1.0 / stride) / t_cpu
+        # CPU baseline: the oracle on one host core (the reference loop is sequential, Renderer.swift:222), about 10 s
+        # of CPU work: calibrate on a 1/8 sample, then whole frames (or the largest 1/stride sample that fits)
+        stride0 = 8 if ntris >= 500_000 else 1
+        t_cal = time_oracle(v, i, xf, W, H, 1, 1, stride0)
+        full_s = t_cal * stride0
+        stride = 1
+        while full_s / stride > 15.0:
+            stride *= 2
+        nframes = int(max(1, min(2000, 10.0 / max(full_s / stride, 1e-4))))
+        t_cpu = time_oracle(v, i, xf, W, H, 1, nframes, stride)
+        cpu_value = (nframes / stride) / t_cpu
         line = {
             "metric": "frames_per_second", "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -323,8 +330,9 @@ def run_cuda(args):
                          "kernel_ms": top_ms, "peak_kind": peak_kind},
             "kernel_ms": acc,
             "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": 1, "kind": "port",
-                             "sample": f"1 render pass of every {stride}-th triangle ({ntris // stride} tris) on 1 core, "
-                                       f"{t_cpu:.2f} s, scaled x{stride}; host has {cpu_count()} cores"},
+                             "sample": f"{nframes} render pass(es) of every {stride}-th triangle ({ntris // stride} of {ntris} "
+                                       f"tris, full clear) on 1 core, {t_cpu:.2f} s in total, each pass counted as 1/{stride} "
+                                       f"frame; host has {cpu_count()} cores"},
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": 8 * W * H,
                     "api": "sr_render_batch, 16 frames per call, pinned host images, mesh uploaded once by sr_set_mesh",
                     "sync_per_frame": {"value": e2e_sync, "unit": "frames/s", "api": "sr_render, one synchronous call per frame"}},
