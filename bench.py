@@ -298,7 +298,7 @@ def run_cuda(args):
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get(args.workload, {}).get(top)
+                traffic = json.load(open(tp)).get(args.workload + ("_depth" if args.depth_test else ""), {}).get(top)
             except Exception:
                 traffic = None
         frame_bytes = S.algorithmic_bytes(ntris, nverts, W, H)
