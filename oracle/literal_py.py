@@ -2,8 +2,8 @@
 
 TEST INFRASTRUCTURE ONLY.  It exists to pin oracle/sr_oracle.cpp: it was written from the Swift source alone
 (/root/reference/renderer/Renderer.swift, cited per function as R:line) without looking at the C++ restatement,
-keeps the reference's per-pixel structure (the 2x2 inverse is recomputed for every pixel, rows and spans are not
-clipped), and is only usable on small cases (pure-Python loops).  tests/golden/make_golden.py runs both
+keeps the reference's per-pixel structure (the 2x2 inverse is recomputed for every pixel; off-screen rows and pixels,
+which the reference rejects one by one at R:246-250, are stepped over), and is only usable on small cases.  tests/golden/make_golden.py runs both
 restatements on the same inputs and refuses to write fixtures unless they agree bit for bit.
 
 Apple `simd` operations that are not in the reference tree are defined exactly as in oracle/sr_oracle.h:
@@ -54,7 +54,8 @@ def apply(m_cols, xyz):
     acc = [F(m_cols[0][r] * v[0]) for r in range(4)]
     for c in (1, 2, 3):
         acc = [F(acc[r] + F(m_cols[c][r] * v[c])) for r in range(4)]
-    return F(acc[0] / acc[3]), F(acc[1] / acc[3]), F(acc[2] / acc[3])
+    with np.errstate(all="ignore"):                             # w = 0 gives inf/NaN, caught by the domain rule
+        return F(acc[0] / acc[3]), F(acc[1] / acc[3]), F(acc[2] / acc[3])
 
 
 def converted_to_screen(xyz, width, height):
