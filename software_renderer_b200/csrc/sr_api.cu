@@ -61,8 +61,11 @@ struct sr_ctx {
     // adaptive policy (depth off): index-descending batches pay off when most tile-list entries are never read
     bool batched_mode = false;
     unsigned long long single_batch_pairs = 0;
-    int force_batches = -1;
-    bool use_pdl = true;                 // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
+    int force_batches = -1;              // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
+    bool use_pdl = true;
+    // speculative frames without the binning kernels: enabled after a frame in which no triangle was large; a frame
+    // that does meet a large triangle only counts it and is re-run with the full pipeline (results identical)
+    bool nobin_mode = false, call_nobin = false, allow_nobin = true;   // SR_NOBIN=0 disables
     DevBuf<ViewStatus> status;
     ViewStatus* h_status = nullptr;
     size_t h_status_cap = 0;
@@ -223,6 +226,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
         fp.epoch = ++c->frame_epoch;
         fp.batched = (!depth_mode && c->batched_mode && ntris >= (1 << 16)) ? 1 : 0;
+        fp.nobin = (c->nobin_mode && c->allow_nobin && !fp.batched) ? 1 : 0;
+        if (fp.nobin) c->call_nobin = true;
         const int ncnt = fp.ntiles * NCHUNK;
         // index-descending batches from the top: T/8, T/8, 3T/4 (the last one usually finds every tile retired);
         // one batch otherwise
@@ -245,13 +250,15 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 else            launch_pdl(c, k_setup<false>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
                 c->launches++;
             }
-            const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
-            c->epoch++;
-            prof_mark(c, st, "k_scan");
-            launch_pdl(c, k_scan, nblocks, SCAN_THREADS, st, c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, fp, bp.index, d_status);
-            c->ticket_base += nblocks;
-            c->launches++;
-            if (n > 0) {
+            if (!fp.nobin) {
+                const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
+                c->epoch++;
+                prof_mark(c, st, "k_scan");
+                launch_pdl(c, k_scan, nblocks, SCAN_THREADS, st, c->counts.p, c->cursor.p, ncnt, c->look.p, c->ticket.p, c->ticket_base, c->epoch, fp, bp.index, d_status);
+                c->ticket_base += nblocks;
+                c->launches++;
+            }
+            if (n > 0 && !fp.nobin) {
                 prof_mark(c, st, "k_bin_fill");
                 const unsigned grid = std::min<unsigned>(div_up(n, 256), 148 * 8);
                 launch_pdl(c, k_bin_fill, grid, 256, st, c->recs.p, d_status, fp, bp, c->cursor.p, c->pairs.p, c->tile_done.p);
@@ -306,8 +313,11 @@ int collect_status(sr_ctx* c, size_t nviews, cudaStream_t st, std::vector<size_t
         unsigned most = 0;
         for (int b = 0; b < MAX_BATCHES; ++b) most = std::max(most, s.total_pairs[b]);
         if (most > c->pairs.cap) { rerun->push_back(i); need = std::max(need, most); }
+        else if (c->call_nobin && s.n_large[0] > 0) { rerun->push_back(i); c->stats.nobin_reruns++; }   // speculation failed
     }
-    if (!rerun->empty()) {
+    if (c->call_nobin && !rerun->empty()) c->nobin_mode = false;
+    c->call_nobin = false;
+    if (need > 0) {
         size_t want = (size_t)need + need / 4 + 1024;
         if (want > 0xFFFFFFF0ull) return fail(c, SR_ERR_CUDA, "tile lists exceed 2^32 entries");
         SR_CUDA(c, c->pairs.reserve(want));
@@ -330,6 +340,10 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
     // adaptive policy for the next call (results are identical either way): batch when most list entries of a
     // single-batch frame were never read; go back when batching did not retire the frame early
     if (prim == SR_TRIANGLE && nviews > 0) {
+        bool any_large = false;
+        for (size_t i = 0; i < nviews; ++i)
+            for (int b = 0; b < MAX_BATCHES; ++b) any_large |= c->h_status[i].n_large[b] != 0;
+        c->nobin_mode = !any_large;
         const ViewStatus& s = c->h_status[nviews - 1];
         if (c->force_batches >= 0) c->batched_mode = c->force_batches != 0;
         else if (!c->batched_mode) {
@@ -392,6 +406,7 @@ int sr_create(sr_ctx** out, int device) {
     sr_ctx* c = new sr_ctx();
     c->device = device;
     if (const char* e = getenv("SR_PDL")) c->use_pdl = atoi(e) != 0;
+    if (const char* e = getenv("SR_NOBIN")) c->allow_nobin = atoi(e) != 0;
     if (const char* e = getenv("SR_BATCHES")) { c->force_batches = atoi(e); c->batched_mode = c->force_batches > 0; }
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
@@ -472,6 +487,7 @@ int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64
     c->has_mesh = true;
     c->batched_mode = c->force_batches > 0;      // the adaptive policy starts over with every mesh
     c->single_batch_pairs = 0;
+    c->nobin_mode = false;
     return rc;
 }
 

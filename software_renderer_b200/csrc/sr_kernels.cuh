@@ -123,6 +123,8 @@ struct FrameParams {
     unsigned pair_capacity;
     unsigned epoch;           // frame stamp for tile_done[]
     int batched;              // 1: several index-descending batches (depth off only)
+    int nobin;                // 1: speculative frame without binning kernels (the previous frame had no large
+                              //    triangle); a large triangle is only counted and the host re-runs the frame
 };
 struct BatchParams {
     int lo, hi;               // primitive range [lo, hi) of this batch
@@ -173,14 +175,17 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     __shared__ StagedRect s_rect[256];
     __shared__ BaryT s_bt[DEPTH ? 256 : 1];
     __shared__ float s_z[DEPTH ? 256 : 1][3];
+    __shared__ unsigned s_nsmall;
 
     if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
     if (fp.batched && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&status->batches_run, 1u);
+    if (threadIdx.x == 0) s_nsmall = 0;
+    __syncthreads();
 
     const int prim = bp.lo + blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
     const bool valid = prim < bp.hi;
-    bool skipped = false, small = false, large = false;
+    bool skipped = false, tiny = false, small = false, large = false;
     SortedTri s = {};
     int ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, y0 = 0, y1 = -1, xmin = 0, xmax = -1;
     unsigned perm = 0;
@@ -201,12 +206,36 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
             xmin = max(min(ax, min(bx, cx)), 0);
             xmax = min(max(ax, max(bx, cx)), fp.width - 1);
             if (y0 <= y1 && xmin <= xmax) {
-                small = (y1 - y0 < SMALL_MAX) && (xmax - xmin < SMALL_MAX);
-                large = !small;
+                // tiny: UNCLIPPED bbox at most 2x2 pixels -> at most three pixels, none of which needs a division
+                tiny = (s.y2 - s.y0 <= 1) && (max(ax, max(bx, cx)) - min(ax, min(bx, cx)) <= 1);
+                small = !tiny && (y1 - y0 < SMALL_MAX) && (xmax - xmin < SMALL_MAX);
+                large = !tiny && !small;
             }
             if (DEPTH && small) {
                 s_bt[threadIdx.x] = bary_setup(ax, ay, bx, by, cx, cy);
                 s_z[threadIdx.x][0] = a.z; s_z[threadIdx.x][1] = b.z; s_z[threadIdx.x][2] = c.z;
+            }
+            if (tiny) {
+                // rows of R:275 are y0 (and y2 = y0 + 1).  Row y0: left = x2 if y2 == y0 (R:470-471, R:478-480), else
+                // x1 if y1 == y0 (nt == 0 on edge s1->s2), else x0; right = x0 (R:486-488 or nt == 0).
+                // Row y2 != y0: left = s2.x (R:478-480), right = x0 + diff*dy/dy = s2.x.
+                BaryT bt;
+                if (DEPTH) bt = bary_setup(ax, ay, bx, by, cx, cy);
+                auto plot = [&](int x, int y) {
+                    if ((unsigned)x >= (unsigned)fp.width || (unsigned)y >= (unsigned)fp.height) return;   // R:246-250
+                    if (fp.batched && tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] == fp.epoch) return;
+                    const size_t o = (size_t)y * fp.width + x;
+                    if (DEPTH) {
+                        const float d = blend3(a.z, b.z, c.z, bary_weights(bt, x, y));
+                        if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, (unsigned)prim));
+                    } else {
+                        atomicMax(vis32 + o, (unsigned)prim + 1u);
+                    }
+                };
+                const int l0 = s.y2 == s.y0 ? s.x2 : (s.y1 == s.y0 ? s.x1 : s.x0);
+                plot(l0, s.y0);
+                if (l0 != s.x0) plot(s.x0, s.y0);
+                if (s.y2 != s.y0) plot(s.x2, s.y2);
             }
         }
     }
@@ -224,57 +253,64 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     const unsigned m_skip = __ballot_sync(0xffffffffu, skipped);
     const unsigned m_small = __ballot_sync(0xffffffffu, small);
     const unsigned m_large = __ballot_sync(0xffffffffu, large);
+    const unsigned m_tiny = __ballot_sync(0xffffffffu, tiny);
     unsigned base = 0;
     if (lane == 0) {
         if (m_skip) atomicAdd(&status->domain_skipped, __popc(m_skip));
-        if (m_small) atomicAdd(&status->n_small, __popc(m_small));
+        if (m_small | m_tiny) atomicAdd(&s_nsmall, __popc(m_small) + __popc(m_tiny));
         if (m_large) base = atomicAdd(&status->n_large[bp.index], __popc(m_large));
     }
-    base = __shfl_sync(0xffffffffu, base, 0);
-    unsigned slot = 0;
-    if (large) {
-        slot = base + __popc(m_large & ((1u << lane) - 1u));
-        recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm,
-                            edge_magic(s.y1 - s.y0), edge_magic(s.y2 - s.y1), edge_magic(s.y2 - s.y0), 0ull};
-    }
-    s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0};
-    // chunks are stored in DESCENDING index order inside each tile list
-    const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
-    s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
-    __syncwarp();
     const int wbase = threadIdx.x & ~31;
-
-    // (a) large triangles: one item per bbox tile -> counts[tile][chunk]++
-    warp_balance(large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0, [&](int src, int item) {
-        const StagedRect r = s_rect[wbase + src];
-        const int w = r.w & 0xffff, cs = r.w >> 16;
-        const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
-        const int tile = ty * fp.tiles_x + tx;
-        if (fp.batched && tile_done[tile] == fp.epoch) return;
-        atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
-    });
+    if (m_large && !fp.nobin) {                              // warp-uniform
+        base = __shfl_sync(0xffffffffu, base, 0);
+        unsigned slot = 0;
+        if (large) {
+            slot = base + __popc(m_large & ((1u << lane) - 1u));
+            recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm,
+                                edge_magic(s.y1 - s.y0), edge_magic(s.y2 - s.y1), edge_magic(s.y2 - s.y0), 0ull};
+        }
+        // chunks are stored in DESCENDING index order inside each tile list
+        const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
+        s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
+        __syncwarp();
+        // (a) large triangles: one item per bbox tile -> counts[tile][chunk]++
+        warp_balance(large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0, [&](int src, int item) {
+            const StagedRect r = s_rect[wbase + src];
+            const int w = r.w & 0xffff, cs = r.w >> 16;
+            const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
+            const int tile = ty * fp.tiles_x + tx;
+            if (fp.batched && tile_done[tile] == fp.epoch) return;
+            atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
+        });
+    }
 
     // (b) small triangles: one item per clipped row -> global atomics on the visibility words
-    warp_balance(small ? (y1 - y0 + 1) : 0, [&](int src, int item) {
-        const StagedTri t = s_tri[wbase + src];
-        const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
-        const int y = t.ystart + item;
-        int l, r;
-        span_row(st, y, l, r);                               // R:276-280
-        l = max(l, 0);
-        r = min(r, fp.width - 1);
-        for (int x = l; x <= r; ++x) {                       // R:281
-            if (fp.batched && tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] == fp.epoch) continue;
-            const size_t o = (size_t)y * fp.width + x;
-            if (DEPTH) {
-                const float3 w = bary_weights(s_bt[wbase + src], x, y);
-                const float d = blend3(s_z[wbase + src][0], s_z[wbase + src][1], s_z[wbase + src][2], w);
-                if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, t.prim));
-            } else {
-                atomicMax(vis32 + o, t.prim + 1u);
+    if (m_small) {                                           // warp-uniform
+        s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0};
+        __syncwarp();
+        warp_balance(small ? (y1 - y0 + 1) : 0, [&](int src, int item) {
+            const StagedTri t = s_tri[wbase + src];
+            const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
+            const int y = t.ystart + item;
+            int l, r;
+            span_row(st, y, l, r);                               // R:276-280
+            l = max(l, 0);
+            r = min(r, fp.width - 1);
+            for (int x = l; x <= r; ++x) {                       // R:281
+                if (fp.batched && tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] == fp.epoch) continue;
+                const size_t o = (size_t)y * fp.width + x;
+                if (DEPTH) {
+                    const float3 w = bary_weights(s_bt[wbase + src], x, y);
+                    const float d = blend3(s_z[wbase + src][0], s_z[wbase + src][1], s_z[wbase + src][2], w);
+                    if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, t.prim));
+                } else {
+                    atomicMax(vis32 + o, t.prim + 1u);
+                }
             }
-        }
-    });
+        });
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && s_nsmall) atomicAdd(&status->n_small, s_nsmall);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -494,8 +530,8 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
     }
 
     const size_t seg = (size_t)tile * NCHUNK;
-    const unsigned begin = seg == 0 ? 0u : cursor[seg - 1];
-    const unsigned end = min(cursor[seg + NCHUNK - 1], fp.pair_capacity);
+    const unsigned begin = fp.nobin ? 0u : (seg == 0 ? 0u : cursor[seg - 1]);          // nobin: no tile lists exist
+    const unsigned end = fp.nobin ? 0u : min(cursor[seg + NCHUNK - 1], fp.pair_capacity);
     unsigned p = begin;
     const int x_lo = tx * TILE, x_hi = min(tx * TILE + TILE - 1, fp.width - 1);
     const int yy = ty * TILE + row;

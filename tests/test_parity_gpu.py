@@ -273,3 +273,57 @@ def test_adaptive_policy_switches_and_stays_exact(renderer):
     v, i = S.icosphere(5)
     for k in range(3):
         assert_same(renderer, v, i, S.app_transform(0.1 * k), 1280, 720)
+
+
+@pytest.mark.parametrize("depth_test", [False, True])
+def test_nobin_speculation_and_rerun(depth_test):
+    """After a frame without large triangles the binning kernels are not launched; a later frame that does meet a
+    large triangle is re-run with the full pipeline.  Every frame stays bit-exact."""
+    r = srb.CudaRenderer(0)
+    try:
+        v, i = S.cube_sphere(40)                     # 19,200 triangles
+        zoom = lambda s: (np.diag([s, s, 1.0, 1.0]).astype(np.float32) @ S.app_transform(0.3)).astype(np.float32)
+        W, H = 640, 640
+        assert_same(r, v, i, zoom(0.25), W, H, depth_test=depth_test)          # everything small: full pipeline, then speculate
+        assert r.stats()["binned_tris"] == 0
+        n_full = r.stats()["gpu_launches"]
+        assert_same(r, v, i, zoom(0.26), W, H, depth_test=depth_test)          # speculative frame: fewer launches
+        assert r.stats()["gpu_launches"] < n_full and r.stats()["nobin_reruns"] == 0
+        assert_same(r, v, i, zoom(1.5), W, H, depth_test=depth_test)           # large triangles appear: re-run
+        assert r.stats()["nobin_reruns"] == 1 and r.stats()["binned_tris"] > 0
+        assert_same(r, v, i, zoom(1.5), W, H, depth_test=depth_test)           # policy went back to the full pipeline
+        assert r.stats()["nobin_reruns"] == 0
+        views = np.stack([zoom(s) for s in (0.2, 0.25, 1.2, 0.22)])            # a batch in which one view fails
+        assert_same(r, v, i, zoom(0.2), W, H, depth_test=depth_test)           # all small again -> speculate next call
+        r.depth_test = depth_test
+        color, depth = r.render_views(views, W, H)
+        assert r.stats()["nobin_reruns"] == 1
+        r.depth_test = False
+        for k in range(4):
+            rc, rc_c, rc_d, _ = O.render(v, i, views[k], W, H, flags=O.DEPTH_LESS if depth_test else 0)
+            assert np.array_equal(color[k], rc_c) and np.array_equal(depth[k].view(np.uint32), rc_d.view(np.uint32)), k
+    finally:
+        r.close()
+
+
+def test_tiny_triangle_path_all_shapes(renderer):
+    """Every triangle whose integer corners fit a 2x2 pixel box (the lane-local path of k_setup), in every corner
+    order, plus neighbours that are one pixel wider or taller (the warp-balanced path), both depth modes."""
+    pts = [(x, y) for x in range(3) for y in range(3)]
+    tris = [(a, b, c) for a in pts for b in pts for c in pts]
+    n = len(tris)
+    W = H = 4 * 28
+    xyz = np.zeros((3 * n, 3), np.float32)
+    rng = np.random.default_rng(5)
+    for k, t in enumerate(tris):
+        ox, oy = 4 * (k % 28) + 0.3, 4 * (k // 28) + 0.4
+        for q, (px, py) in enumerate(t):
+            sx, sy = ox + px + 0.2 * q, oy + py + 0.1 * q          # fractional screen coordinates, distinct float y
+            xyz[3 * k + q] = ((sx / W - 0.5) / 0.5, (sy / H - 0.5) / -0.5, rng.uniform(0.1, 0.9))
+    v = S.pack_vertices(xyz, rng.uniform(0, 1, size=(3 * n, 3)).astype(np.float32))
+    i = np.arange(3 * n, dtype=np.int64)
+    for dt in (False, True):
+        assert_same(renderer, v, i, I4, W, H, depth_test=dt)
+    # the same shapes hanging over the image border
+    shift = np.eye(4, dtype=np.float32); shift[0, 3] = -1.0 + 1.0 / W; shift[1, 3] = 1.0 - 1.0 / H
+    assert_same(renderer, v, i, shift, W, H)
