@@ -15,6 +15,7 @@ using namespace sr;
 namespace {
 
 constexpr int MAX_PROF = 64;
+constexpr size_t kSlabLimit = 4ull << 30;
 
 template <class T>
 struct DevBuf {
@@ -66,6 +67,12 @@ struct sr_ctx {
     // speculative frames without the binning kernels: enabled after a frame in which no triangle was large; a frame
     // that does meet a large triangle only counts it and is re-run with the full pipeline (results identical)
     bool nobin_mode = false, call_nobin = false, allow_nobin = true;   // SR_NOBIN=0 disables
+    // tile lists as fixed-capacity slabs (k_setup fills them directly; no k_scan / k_bin_fill).  A segment that
+    // overflows makes the host double the capacity and re-run the frame; past kSlabLimit bytes the context falls
+    // back to compact lists (scan + fill) for good.  SR_SLAB=0 forces compact lists.
+    bool slab_mode = true;
+    unsigned slab_cap = 32, call_slab_cap = 0;
+    size_t last_ntiles = 0;
     DevBuf<ViewStatus> status;
     ViewStatus* h_status = nullptr;
     size_t h_status_cap = 0;
@@ -179,6 +186,11 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
         size_t want = std::min<size_t>(std::max<size_t>(4 * ntris, 1u << 20), 64u << 20);
         SR_CUDA(c, c->pairs.reserve(want));
     }
+    if (c->slab_mode) {
+        const size_t need = ncnt * c->slab_cap;
+        if (need * sizeof(unsigned) > kSlabLimit) c->slab_mode = false;
+        else SR_CUDA(c, c->pairs.reserve(need));
+    }
     if (depth_mode) {
         if (npx > c->vis64.cap) {
             SR_CUDA(c, c->vis64.reserve(npx));
@@ -226,6 +238,9 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
         fp.epoch = ++c->frame_epoch;
         fp.batched = (!depth_mode && c->batched_mode && ntris >= (1 << 16)) ? 1 : 0;
+        fp.slab_cap = (c->slab_mode && (size_t)fp.ntiles * NCHUNK * c->slab_cap <= c->pairs.cap) ? (int)c->slab_cap : 0;
+        c->call_slab_cap = (unsigned)fp.slab_cap;
+        c->last_ntiles = (size_t)fp.ntiles;
         fp.nobin = (c->nobin_mode && c->allow_nobin && !fp.batched) ? 1 : 0;
         if (fp.nobin) c->call_nobin = true;
         const int ncnt = fp.ntiles * NCHUNK;
@@ -246,11 +261,11 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             while (n > 0 && ((n - 1) >> bp.chunk_shift) >= NCHUNK) bp.chunk_shift++;
             if (n > 0) {
                 prof_mark(c, st, "k_setup");
-                if (depth_mode) launch_pdl(c, k_setup<true>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
-                else            launch_pdl(c, k_setup<false>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->tile_done.p, d_status);
+                if (depth_mode) launch_pdl(c, k_setup<true>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->pairs.p, c->tile_done.p, d_status);
+                else            launch_pdl(c, k_setup<false>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->pairs.p, c->tile_done.p, d_status);
                 c->launches++;
             }
-            if (!fp.nobin) {
+            if (!fp.nobin && !fp.slab_cap) {
                 const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
                 c->epoch++;
                 prof_mark(c, st, "k_scan");
@@ -258,7 +273,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 c->ticket_base += nblocks;
                 c->launches++;
             }
-            if (n > 0 && !fp.nobin) {
+            if (n > 0 && !fp.nobin && !fp.slab_cap) {
                 prof_mark(c, st, "k_bin_fill");
                 const unsigned grid = std::min<unsigned>(div_up(n, 256), 148 * 8);
                 launch_pdl(c, k_bin_fill, grid, 256, st, c->recs.p, d_status, fp, bp, c->cursor.p, c->pairs.p, c->tile_done.p);
@@ -267,8 +282,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             prof_mark(c, st, "k_tile");
             // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
             const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;
-            if (depth_mode) launch_pdl(c, k_tile<true>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
-            else            launch_pdl(c, k_tile<false>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            if (depth_mode) launch_pdl(c, k_tile<true>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            else            launch_pdl(c, k_tile<false>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
             c->launches++;
         }
     } else {
@@ -314,6 +329,23 @@ int collect_status(sr_ctx* c, size_t nviews, cudaStream_t st, std::vector<size_t
         for (int b = 0; b < MAX_BATCHES; ++b) most = std::max(most, s.total_pairs[b]);
         if (most > c->pairs.cap) { rerun->push_back(i); need = std::max(need, most); }
         else if (c->call_nobin && s.n_large[0] > 0) { rerun->push_back(i); c->stats.nobin_reruns++; }   // speculation failed
+    }
+    if (c->call_slab_cap) {
+        unsigned seg = 0;
+        for (size_t i = 0; i < nviews; ++i) {
+            const unsigned m = c->h_status[i].seg_max;
+            if (m > c->call_slab_cap) {
+                if (std::find(rerun->begin(), rerun->end(), i) == rerun->end()) rerun->push_back(i);
+                seg = std::max(seg, m);
+            }
+        }
+        if (seg) {
+            unsigned cap = c->slab_cap;
+            while (cap < seg + seg / 4) cap *= 2;
+            c->stats.bin_regrows++;
+            if (c->last_ntiles * NCHUNK * (size_t)cap * sizeof(unsigned) > kSlabLimit) c->slab_mode = false;
+            else { c->slab_cap = cap; SR_CUDA(c, c->pairs.reserve(c->last_ntiles * NCHUNK * (size_t)cap)); }
+        }
     }
     if (c->call_nobin && !rerun->empty()) c->nobin_mode = false;
     c->call_nobin = false;
@@ -406,6 +438,8 @@ int sr_create(sr_ctx** out, int device) {
     sr_ctx* c = new sr_ctx();
     c->device = device;
     if (const char* e = getenv("SR_PDL")) c->use_pdl = atoi(e) != 0;
+    if (const char* e = getenv("SR_SLAB")) c->slab_mode = atoi(e) != 0;
+    if (const char* e = getenv("SR_SLAB_CAP")) c->slab_cap = std::max(1, atoi(e));
     if (const char* e = getenv("SR_NOBIN")) c->allow_nobin = atoi(e) != 0;
     if (const char* e = getenv("SR_BATCHES")) { c->force_batches = atoi(e); c->batched_mode = c->force_batches > 0; }
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&

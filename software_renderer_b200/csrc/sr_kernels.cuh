@@ -30,7 +30,10 @@ constexpr int MAX_BATCHES = 8;       // index-descending batches per frame (dept
 constexpr int SMALL_MAX = 8;         // direct path: clipped bbox at most SMALL_MAX x SMALL_MAX pixels
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;        // per thread -> 2048 counters per CTA
-constexpr int TILE_BATCH = 16;       // triangles per coverage batch in k_tile
+constexpr int TILE_BATCH = 16;
+#ifndef SR_TILE_MINB
+#define SR_TILE_MINB 5
+#endif       // triangles per coverage batch in k_tile
 
 // Per-view counters, read back by the host after the frame.
 struct ViewStatus {
@@ -41,7 +44,8 @@ struct ViewStatus {
     unsigned tiles_done;                // tiles shaded before the final batch (batched mode)
     unsigned batches_run;               // batches that still had unfinished tiles when they started
     unsigned long long pairs_consumed;  // pairs the tile kernel actually processed (early-out feedback)
-    unsigned long long _pad;
+    unsigned seg_max;                   // slab lists: largest (tile, chunk) segment requested (> slab_cap -> frame is re-run)
+    unsigned open_after_first;          // batched mode: tiles still open after the first batch
 };
 
 // Bin-list record of a large triangle (64 B): corners SORTED as R:271 leaves them, the sort permutation (to get
@@ -123,6 +127,8 @@ struct FrameParams {
     unsigned pair_capacity;
     unsigned epoch;           // frame stamp for tile_done[]
     int batched;              // 1: several index-descending batches (depth off only)
+    int slab_cap;             // > 0: tile lists are fixed-capacity slabs, slab_cap entries per (tile, chunk) segment,
+                              //      filled directly by k_setup (no k_scan / k_bin_fill); 0: compact lists
     int nobin;                // 1: speculative frame without binning kernels (the previous frame had no large
                               //    triangle); a large triangle is only counted and the host re-runs the frame
 };
@@ -168,8 +174,8 @@ template <bool DEPTH>
 __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, const float4* __restrict__ sv, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
-                                               unsigned* __restrict__ counts, const unsigned* __restrict__ tile_done,
-                                               ViewStatus* __restrict__ status) {
+                                               unsigned* __restrict__ counts, unsigned* __restrict__ pairs,
+                                               const unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
     pdl_wait();
     __shared__ StagedTri s_tri[256];
     __shared__ StagedRect s_rect[256];
@@ -273,15 +279,58 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
         const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
         s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
         __syncwarp();
-        // (a) large triangles: one item per bbox tile -> counts[tile][chunk]++
-        warp_balance(large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0, [&](int src, int item) {
-            const StagedRect r = s_rect[wbase + src];
-            const int w = r.w & 0xffff, cs = r.w >> 16;
-            const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
-            const int tile = ty * fp.tiles_x + tx;
-            if (fp.batched && tile_done[tile] == fp.epoch) return;
-            atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
-        });
+        // (a) large triangles: one item per bbox tile.
+        //   compact lists: counts[tile][chunk]++ here, k_scan + k_bin_fill build the lists afterwards
+        //   slab lists   : the returned count IS the position inside the fixed-capacity segment of (tile, chunk);
+        //                  four atomics per lane are in flight before the first dependent store
+        const int items = large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0;
+        if (!fp.slab_cap) {
+            warp_balance(items, [&](int src, int item) {
+                const StagedRect r = s_rect[wbase + src];
+                const int w = r.w & 0xffff, cs = r.w >> 16;
+                const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
+                const int tile = ty * fp.tiles_x + tx;
+                if (fp.batched && tile_done[tile] == fp.epoch) return;
+                atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
+            });
+        } else {
+            int incl = items;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += t; }
+            const int excl = incl - items;
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            unsigned seg_max = 0;
+            for (int b0 = 0; b0 < total; b0 += 128) {
+                unsigned pos[4], seg[4], val[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int k = b0 + u * 32 + (int)lane;
+                    int j = 0;
+#pragma unroll
+                    for (int step = 16; step > 0; step >>= 1) {
+                        const int e = __shfl_sync(0xffffffffu, excl, j + step);
+                        if (e <= k) j += step;
+                    }
+                    const int ej = __shfl_sync(0xffffffffu, excl, j);
+                    pos[u] = 0xffffffffu;
+                    if (k < total) {
+                        const StagedRect r = s_rect[wbase + j];
+                        const int item = k - ej, w = r.w & 0xffff, cs = r.w >> 16;
+                        const int tile = (r.ty0 + item / w) * fp.tiles_x + r.tx0 + item % w;
+                        val[u] = (unsigned)r.slot;
+                        seg[u] = (unsigned)tile * NCHUNK + cs;
+                        if (!(fp.batched && tile_done[tile] == fp.epoch)) pos[u] = atomicAdd(&counts[seg[u]], 1u);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (pos[u] == 0xffffffffu) continue;
+                    if (pos[u] < (unsigned)fp.slab_cap) pairs[(size_t)seg[u] * fp.slab_cap + pos[u]] = val[u];
+                    else seg_max = max(seg_max, pos[u] + 1u);
+                }
+            }
+            if (seg_max) atomicMax(&status->seg_max, seg_max);      // a segment overflowed: the host grows the slabs and re-runs
+        }
     }
 
     // (b) small triangles: one item per clipped row -> global atomics on the visibility words
@@ -497,9 +546,9 @@ __device__ __forceinline__ void shade_pixel(const ShadeIn& in, unsigned prim, in
 }
 
 template <bool DEPTH>
-__global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
-                                              const unsigned* __restrict__ cursor, const unsigned* __restrict__ pairs,
-                                              unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
+__global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
+                                              const unsigned* __restrict__ cursor, unsigned* __restrict__ counts,
+                                              const unsigned* __restrict__ pairs, unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
                                               unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status,
                                               unsigned* __restrict__ color_out, float* __restrict__ depth_out) {
     pdl_wait();
@@ -508,6 +557,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
     __shared__ TriRec s_rec[2][TILE_BATCH];
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
+    __shared__ unsigned s_off[NCHUNK + 1];                 // slab lists: prefix of the tile's 16 segment lengths
 
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
@@ -530,11 +580,43 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
     }
 
     const size_t seg = (size_t)tile * NCHUNK;
-    const unsigned begin = fp.nobin ? 0u : (seg == 0 ? 0u : cursor[seg - 1]);          // nobin: no tile lists exist
-    const unsigned end = fp.nobin ? 0u : min(cursor[seg + NCHUNK - 1], fp.pair_capacity);
-    unsigned p = begin;
+    const bool slab = fp.slab_cap > 0 && !fp.nobin;
+    unsigned begin = 0u, end = 0u;                         // nobin: no tile lists exist
+    if (!slab && !fp.nobin) {
+        begin = seg == 0 ? 0u : cursor[seg - 1];
+        end = min(cursor[seg + NCHUNK - 1], fp.pair_capacity);
+    }
     const int x_lo = tx * TILE, x_hi = min(tx * TILE + TILE - 1, fp.width - 1);
     const int yy = ty * TILE + row;
+
+    __syncthreads();                                       // previous tile of this CTA is done with shared memory
+    if (slab) {
+        // the tile's list = its 16 segments, highest index chunk first; lengths are read and re-armed here
+        if (tid < 32) {
+            unsigned c = 0;
+            if (tid < NCHUNK) {
+                c = counts[seg + tid];
+                if (c) counts[seg + tid] = 0u;
+                c = min(c, (unsigned)fp.slab_cap);         // an overflowed segment: the frame is re-run anyway
+            }
+            unsigned inc = c;
+#pragma unroll
+            for (int d = 1; d < NCHUNK; d <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, inc, d); if (tid >= d) inc += t; }
+            if (tid < NCHUNK) s_off[tid + 1] = inc;
+            if (tid == 0) s_off[0] = 0u;
+        }
+        __syncthreads();
+        end = s_off[NCHUNK];
+        if (tid == 0 && end) atomicAdd(&status->total_pairs[bp.index], end);
+    }
+    unsigned p = begin;
+    auto pair_at = [&](unsigned q) -> unsigned {
+        if (!slab) return pairs[q];
+        int c = 0;
+#pragma unroll
+        for (int step = NCHUNK / 2; step > 0; step >>= 1) if (s_off[c + step] <= q) c += step;
+        return pairs[(seg + c) * (size_t)fp.slab_cap + (q - s_off[c])];
+    };
 
     // software pipeline: records of the NEXT batch travel global -> shared with cp.async (no registers held) while
     // the current batch is processed; the slot indices are fetched one batch further ahead.
@@ -543,10 +625,9 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
                                              reinterpret_cast<const char*>(recs + slot) + 16 * row, 16);
     };
     unsigned slot_next = 0;
-    __syncthreads();                                       // previous tile of this CTA is done with shared memory
-    if (p + j < end && row < 4) fetch(0, pairs[p + j]);
+    if (p + j < end && row < 4) fetch(0, pair_at(p + j));
     __pipeline_commit();
-    if (p + TILE_BATCH + j < end && row < 4) slot_next = pairs[p + TILE_BATCH + j];
+    if (p + TILE_BATCH + j < end && row < 4) slot_next = pair_at(p + TILE_BATCH + j);
     int cur = 0;
     __pipeline_wait_prior(0);
     __syncthreads();                                       // s_rec[0] complete
@@ -555,7 +636,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : 6) k_tile(FrameParams fp, Bat
         const int n = min((unsigned)TILE_BATCH, end - p);
         if (p + TILE_BATCH + j < end) fetch(cur ^ 1, slot_next);
         __pipeline_commit();
-        if (p + 2 * TILE_BATCH + j < end && row < 4) slot_next = pairs[p + 2 * TILE_BATCH + j];
+        if (p + 2 * TILE_BATCH + j < end && row < 4) slot_next = pair_at(p + 2 * TILE_BATCH + j);
         {   // phase A: (triangle j, row) -> column mask
             unsigned mask = 0;
             if (j < n) {
