@@ -54,7 +54,7 @@ struct __align__(16) TriRec {
     int x0, y0, x1, y1, x2, y2;
     unsigned prim;
     unsigned perm;                       // sorted position k holds original corner (perm >> 2k) & 3
-    unsigned long long m01, m12, m02;    // edge_magic(y1-y0), (y2-y1), (y2-y0)
+    double r01, r12, r02;                // edge_rcp(y1-y0), (y2-y1), (y2-y0)
     unsigned long long _pad;
 };
 
@@ -162,7 +162,14 @@ __device__ __forceinline__ void warp_balance(int n, F&& f) {
     }
 }
 
-struct __align__(16) StagedTri { int x0, y0, x1, y1, x2, y2; unsigned prim; int ystart; };   // sorted corners
+// item -> (item / w, item % w) for 0 <= item < 2^23, 1 <= w: float estimate (off by at most one), exact correction
+__device__ __forceinline__ void divmod_tiles(int item, int w, int& q, int& r) {
+    q = __float2int_rz(__fmul_rn(__int2float_rn(item), __frcp_rn(__int2float_rn(w))));
+    r = item - q * w;
+    if (r < 0) { --q; r += w; } else if (r >= w) { ++q; r -= w; }
+}
+
+struct __align__(16) StagedTri { int x0, y0, x1, y1, x2, y2; unsigned prim; int ystart; double r01, r12, r02; double _pad; };   // sorted corners + edge reciprocals
 struct __align__(16) StagedRect { int tx0, ty0, w, slot; };                                   // tile rectangle; w | cslot<<16
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -268,12 +275,13 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     }
     const int wbase = threadIdx.x & ~31;
     if (m_large && !fp.nobin) {                              // warp-uniform
-        base = __shfl_sync(0xffffffffu, base, 0);
-        unsigned slot = 0;
+        // slab lists: the record of triangle `prim` lives at recs[prim - batch start] (nothing waits for the counter);
+        // compact lists: records are compacted, k_bin_fill walks them
+        unsigned slot = (unsigned)(prim - bp.lo);
+        if (!fp.slab_cap) slot = __shfl_sync(0xffffffffu, base, 0) + __popc(m_large & ((1u << lane) - 1u));
         if (large) {
-            slot = base + __popc(m_large & ((1u << lane) - 1u));
             recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm,
-                                edge_magic(s.y1 - s.y0), edge_magic(s.y2 - s.y1), edge_magic(s.y2 - s.y0), 0ull};
+                                edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), 0ull};
         }
         // chunks are stored in DESCENDING index order inside each tile list
         const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
@@ -288,8 +296,9 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
             warp_balance(items, [&](int src, int item) {
                 const StagedRect r = s_rect[wbase + src];
                 const int w = r.w & 0xffff, cs = r.w >> 16;
-                const int ty = r.ty0 + item / w, tx = r.tx0 + item % w;
-                const int tile = ty * fp.tiles_x + tx;
+                int qy, qx;
+                divmod_tiles(item, w, qy, qx);
+                const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
                 if (fp.batched && tile_done[tile] == fp.epoch) return;
                 atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
             });
@@ -316,7 +325,9 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
                     if (k < total) {
                         const StagedRect r = s_rect[wbase + j];
                         const int item = k - ej, w = r.w & 0xffff, cs = r.w >> 16;
-                        const int tile = (r.ty0 + item / w) * fp.tiles_x + r.tx0 + item % w;
+                        int qy, qx;
+                        divmod_tiles(item, w, qy, qx);
+                        const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
                         val[u] = (unsigned)r.slot;
                         seg[u] = (unsigned)tile * NCHUNK + cs;
                         if (!(fp.batched && tile_done[tile] == fp.epoch)) pos[u] = atomicAdd(&counts[seg[u]], 1u);
@@ -335,14 +346,15 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
 
     // (b) small triangles: one item per clipped row -> global atomics on the visibility words
     if (m_small) {                                           // warp-uniform
-        s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0};
+        if (small) s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0,
+                                                   edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), 0.0};
         __syncwarp();
         warp_balance(small ? (y1 - y0 + 1) : 0, [&](int src, int item) {
             const StagedTri t = s_tri[wbase + src];
             const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
             const int y = t.ystart + item;
             int l, r;
-            span_row(st, y, l, r);                               // R:276-280
+            span_row_rcp(st, EdgeRcp{t.r01, t.r12, t.r02}, y, l, r);   // R:276-280
             l = max(l, 0);
             r = min(r, fp.width - 1);
             for (int x = l; x <= r; ++x) {                       // R:281
@@ -499,7 +511,9 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
                 if (k < total) {
                     const StagedRect r = s_rect[wbase + j];
                     const int item = k - ej, w = r.w & 0xffff, cs = r.w >> 16;
-                    const int tile = (r.ty0 + item / w) * fp.tiles_x + r.tx0 + item % w;
+                    int qy, qx;
+                    divmod_tiles(item, w, qy, qx);
+                    const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
                     val[u] = (unsigned)r.slot;
                     if (!(fp.batched && tile_done[tile] == fp.epoch))
                         pos[u] = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);
@@ -644,7 +658,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                 const SortedTri s = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                 if (yy >= s.y0 && yy <= s.y2 && yy < fp.height) {
                     int l, r;
-                    span_row_magic(s, EdgeMagic{t.m01, t.m12, t.m02}, yy, l, r);
+                    span_row_rcp(s, EdgeRcp{t.r01, t.r12, t.r02}, yy, l, r);
                     l = max(l, x_lo);
                     r = min(r, x_hi);
                     if (l <= r) mask = ((2u << (r - l)) - 1u) << (l - x_lo);

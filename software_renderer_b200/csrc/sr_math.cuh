@@ -73,28 +73,31 @@ __device__ __forceinline__ void span_row(const SortedTri& s, int t, int& l, int&
 }
 
 // ---- the same rule with per-edge reciprocals ---------------------------------------------------------------------
-// For 0 <= n < 2^31 and 1 <= d < 2^31:  floor(n / d) == umul64hi(n << 2, M) with M = floor(2^62 / d) + 1
-// (error term n * (M*d - 2^62) / (d * 2^62) < 1/d, so the floor never moves).  M is computed once per edge in
-// triangle setup; a row then costs one 64-bit multiply-high instead of an integer division.  Larger numerators
-// (far off-screen corners) fall back to the 64-bit division, so the result is always the reference's quotient.
-__device__ __forceinline__ unsigned long long edge_magic(int dy) {
-    return dy > 0 ? (1ull << 62) / (unsigned long long)dy + 1ull : 0ull;
+// For integers 0 <= n < 2^31 and 1 <= d < 2^31:  floor(n / d) == trunc(fl(double(n) * R)),  R = fl(fl(1/d) * (1 + 2^-40)).
+// R = (1/d)(1 + e) with e in [2^-40 - 2^-51, 2^-40 + 2^-51]; the rounded product is (n/d)(1 + e)(1 + g), |g| <= 2^-53,
+// which is >= n/d (so an exact quotient never drops below its integer) and exceeds n/d by less than
+// n * 2^-39 / d < 1/d, the distance from n/d to the next integer boundary (so the floor never moves up).
+// R is computed once per edge in triangle setup; a row then costs one conversion, one DMUL and one truncation
+// instead of an integer division.  Larger numerators (far off-screen corners) fall back to the 64-bit division,
+// so the result is always the reference's quotient.  tests/test_host_math.py checks the claim on the CPU.
+__device__ __forceinline__ double edge_rcp(int dy) {
+    return dy > 0 ? __dmul_rn(__drcp_rn((double)dy), 1.0 + 0x1p-40) : 0.0;
 }
-__device__ __forceinline__ int lerp_magic(int sx, int sy, int ex, int ey, int t, unsigned long long M) {
-    const long long num = ((long long)ex - (long long)sx) * ((long long)t - (long long)sy);
+__device__ __forceinline__ int lerp_rcp(int sx, int sy, int ex, int ey, int t, double R) {
+    const long long num = (long long)(ex - sx) * (long long)(t - sy);       // |ex - sx|, |t - sy| < 2^31 inside the domain
     const unsigned long long a = (unsigned long long)(num < 0 ? -num : num);
     unsigned long long q;
-    if (a < (1ull << 31)) q = __umul64hi(a << 2, M);
+    if (a < (1ull << 31)) q = (unsigned long long)__double2uint_rz(__dmul_rn((double)(unsigned)a, R));
     else q = a / (unsigned long long)((long long)ey - (long long)sy);
     return (int)((long long)sx + (num < 0 ? -(long long)q : (long long)q));
 }
-struct EdgeMagic { unsigned long long m01, m12, m02; };
-__device__ __forceinline__ void span_row_magic(const SortedTri& s, const EdgeMagic& m, int t, int& l, int& r) {
+struct EdgeRcp { double r01, r12, r02; };
+__device__ __forceinline__ void span_row_rcp(const SortedTri& s, const EdgeRcp& m, int t, int& l, int& r) {
     int a, b;
     if (t >= s.y2) a = s.x2;
-    else if (t >= s.y1) a = lerp_magic(s.x1, s.y1, s.x2, s.y2, t, m.m12);
-    else a = lerp_magic(s.x0, s.y0, s.x1, s.y1, t, m.m01);
-    b = (s.y2 == s.y0) ? s.x0 : lerp_magic(s.x0, s.y0, s.x2, s.y2, t, m.m02);
+    else if (t >= s.y1) a = lerp_rcp(s.x1, s.y1, s.x2, s.y2, t, m.r12);
+    else a = lerp_rcp(s.x0, s.y0, s.x1, s.y1, t, m.r01);
+    b = (s.y2 == s.y0) ? s.x0 : lerp_rcp(s.x0, s.y0, s.x2, s.y2, t, m.r02);
     l = min(a, b);
     r = max(a, b);
 }
