@@ -261,8 +261,9 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             while (n > 0 && ((n - 1) >> bp.chunk_shift) >= NCHUNK) bp.chunk_shift++;
             if (n > 0) {
                 prof_mark(c, st, "k_setup");
-                if (depth_mode) launch_pdl(c, k_setup<true>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->pairs.p, c->tile_done.p, d_status);
-                else            launch_pdl(c, k_setup<false>, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->pairs.p, c->tile_done.p, d_status);
+                auto ks = depth_mode ? (fp.nobin ? k_setup<true, false> : k_setup<true, true>)
+                                     : (fp.nobin ? k_setup<false, false> : k_setup<false, true>);
+                launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->pairs.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             if (!fp.nobin && !fp.slab_cap) {

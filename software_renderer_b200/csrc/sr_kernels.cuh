@@ -177,7 +177,8 @@ struct __align__(16) StagedRect { int tx0, ty0, w, slot; };                     
 // counting of large ones.  Both inner loops (rows of small triangles, tiles of large ones) are re-balanced over
 // the warp, so one big triangle does not serialize 31 idle lanes.
 // ---------------------------------------------------------------------------------------------------------------
-template <bool DEPTH>
+// BIN = false: the speculative no-binning frame (fp.nobin): the large-triangle code is compiled out.
+template <bool DEPTH, bool BIN>
 __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, const float4* __restrict__ sv, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
                                                const unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
     pdl_wait();
     __shared__ StagedTri s_tri[256];
-    __shared__ StagedRect s_rect[256];
+    __shared__ StagedRect s_rect[BIN ? 256 : 1];
     __shared__ BaryT s_bt[DEPTH ? 256 : 1];
     __shared__ float s_z[DEPTH ? 256 : 1][3];
     __shared__ unsigned s_nsmall;
@@ -274,32 +275,51 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
         if (m_large) base = atomicAdd(&status->n_large[bp.index], __popc(m_large));
     }
     const int wbase = threadIdx.x & ~31;
-    if (m_large && !fp.nobin) {                              // warp-uniform
+    const bool binning = BIN && m_large && !fp.nobin;        // warp-uniform
+    if (m_small || binning) {
+        // reciprocals only for binned triangles (used many times); the few rows of a small one mostly hit the
+        // division-free shortcuts of span_row
+        if (large && binning)
+            s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0,
+                                           edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), 0.0};
+        else if (small)
+            s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0, 0.0, 0.0, 0.0, 0.0};
+        __syncwarp();
+    }
+    // bbox tile (tx, ty) of staged triangle `src`: can it hold a covered pixel?  (prunes the corners of the bbox)
+    auto tile_touched = [&](int src, int tx, int ty) -> bool {
+        const StagedTri t = s_tri[wbase + src];
+        const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
+        const int ya = max(max(ty * TILE, t.y0), 0), yb = min(min(ty * TILE + TILE - 1, t.y2), fp.height - 1);
+        return rect_touched(st, EdgeRcp{t.r01, t.r12, t.r02}, tx * TILE, min(tx * TILE + TILE - 1, fp.width - 1), ya, yb);
+    };
+    if (binning) {
         // slab lists: the record of triangle `prim` lives at recs[prim - batch start] (nothing waits for the counter);
         // compact lists: records are compacted, k_bin_fill walks them
         unsigned slot = (unsigned)(prim - bp.lo);
         if (!fp.slab_cap) slot = __shfl_sync(0xffffffffu, base, 0) + __popc(m_large & ((1u << lane) - 1u));
         if (large) {
-            recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm,
-                                edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), 0ull};
+            const StagedTri& t = s_tri[threadIdx.x];
+            recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm, t.r01, t.r12, t.r02, 0ull};
         }
         // chunks are stored in DESCENDING index order inside each tile list
         const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
-        s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
+        const int items = large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0;
+        s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (items > 2 ? 0x8000 : 0) | (cslot << 16), (int)slot};
         __syncwarp();
         // (a) large triangles: one item per bbox tile.
         //   compact lists: counts[tile][chunk]++ here, k_scan + k_bin_fill build the lists afterwards
         //   slab lists   : the returned count IS the position inside the fixed-capacity segment of (tile, chunk);
         //                  four atomics per lane are in flight before the first dependent store
-        const int items = large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0;
         if (!fp.slab_cap) {
             warp_balance(items, [&](int src, int item) {
                 const StagedRect r = s_rect[wbase + src];
-                const int w = r.w & 0xffff, cs = r.w >> 16;
+                const int w = r.w & 0x7fff, cs = r.w >> 16;
                 int qy, qx;
                 divmod_tiles(item, w, qy, qx);
                 const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
                 if (fp.batched && tile_done[tile] == fp.epoch) return;
+                if ((r.w & 0x8000) && !tile_touched(src, r.tx0 + qx, r.ty0 + qy)) return;
                 atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
             });
         } else {
@@ -324,13 +344,15 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
                     pos[u] = 0xffffffffu;
                     if (k < total) {
                         const StagedRect r = s_rect[wbase + j];
-                        const int item = k - ej, w = r.w & 0xffff, cs = r.w >> 16;
+                        const int item = k - ej, w = r.w & 0x7fff, cs = r.w >> 16;
                         int qy, qx;
                         divmod_tiles(item, w, qy, qx);
                         const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
                         val[u] = (unsigned)r.slot;
                         seg[u] = (unsigned)tile * NCHUNK + cs;
-                        if (!(fp.batched && tile_done[tile] == fp.epoch)) pos[u] = atomicAdd(&counts[seg[u]], 1u);
+                        if (!(fp.batched && tile_done[tile] == fp.epoch) &&
+                            (!(r.w & 0x8000) || tile_touched(j, r.tx0 + qx, r.ty0 + qy)))
+                            pos[u] = atomicAdd(&counts[seg[u]], 1u);
                     }
                 }
 #pragma unroll
@@ -346,15 +368,12 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
 
     // (b) small triangles: one item per clipped row -> global atomics on the visibility words
     if (m_small) {                                           // warp-uniform
-        if (small) s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0,
-                                                   edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), 0.0};
-        __syncwarp();
         warp_balance(small ? (y1 - y0 + 1) : 0, [&](int src, int item) {
             const StagedTri t = s_tri[wbase + src];
             const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
             const int y = t.ystart + item;
             int l, r;
-            span_row_rcp(st, EdgeRcp{t.r01, t.r12, t.r02}, y, l, r);   // R:276-280
+            span_row(st, y, l, r);                               // R:276-280
             l = max(l, 0);
             r = min(r, fp.width - 1);
             for (int x = l; x <= r; ++x) {                       // R:281
@@ -483,8 +502,8 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
             const int xmin = max(min(t.x0, min(t.x1, t.x2)), 0), xmax = min(max(t.x0, max(t.x1, t.x2)), fp.width - 1);
             const int cslot = NCHUNK - 1 - (((int)t.prim - bp.lo) >> bp.chunk_shift);
             const int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
-            s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (cslot << 16), (int)slot};
             items = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
+            s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (items > 2 ? 0x8000 : 0) | (cslot << 16), (int)slot};
         }
         __syncwarp();
         // (record, tile) pairs spread over the warp, four per lane per step so that four list-cursor atomics are in
@@ -510,12 +529,20 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
                 pos[u] = 0xffffffffu;
                 if (k < total) {
                     const StagedRect r = s_rect[wbase + j];
-                    const int item = k - ej, w = r.w & 0xffff, cs = r.w >> 16;
+                    const int item = k - ej, w = r.w & 0x7fff, cs = r.w >> 16;
                     int qy, qx;
                     divmod_tiles(item, w, qy, qx);
                     const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
                     val[u] = (unsigned)r.slot;
-                    if (!(fp.batched && tile_done[tile] == fp.epoch))
+                    bool keep = !(fp.batched && tile_done[tile] == fp.epoch);
+                    if (keep && (r.w & 0x8000)) {             // same pruning rule as the counting pass in k_setup
+                        const TriRec& t = recs[r.slot];
+                        const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
+                        const int tx = r.tx0 + qx, ty = r.ty0 + qy;
+                        const int ya = max(max(ty * TILE, t.y0), 0), yb = min(min(ty * TILE + TILE - 1, t.y2), fp.height - 1);
+                        keep = rect_touched(st, EdgeRcp{t.r01, t.r12, t.r02}, tx * TILE, min(tx * TILE + TILE - 1, fp.width - 1), ya, yb);
+                    }
+                    if (keep)
                         pos[u] = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);
                 }
             }

@@ -102,6 +102,21 @@ __device__ __forceinline__ void span_row_rcp(const SortedTri& s, const EdgeRcp& 
     r = max(a, b);
 }
 
+// Can triangle `s` cover a pixel of the rectangle columns [x_lo, x_hi] x rows [ya, yb] (ya..yb inside the triangle's
+// own row range)?  Both span ends are monotone in the row on each edge piece (x + trunc(diff*nt/dy) is monotone in nt,
+// and the pieces join continuously, except that a flat-bottomed triangle (y1 == y2) jumps from near s1.x to s2.x on
+// its last row, R:470-471), so over the rows ya..yb the smallest left end / largest right end are reached at ya, yb,
+// or are bounded by s1.x when the middle corner's row lies in (ya, yb].  The test "min end <= x_hi and max end >= x_lo" never rejects
+// a rectangle that holds a covered pixel; it may keep one that holds none (the two extremes can sit on different rows).
+__device__ __forceinline__ bool rect_touched(const SortedTri& s, const EdgeRcp& m, int x_lo, int x_hi, int ya, int yb) {
+    int l0, r0, l1, r1;
+    span_row_rcp(s, m, ya, l0, r0);
+    span_row_rcp(s, m, yb, l1, r1);
+    int mn = min(l0, l1), mx = max(r0, r1);
+    if (s.y1 > ya && s.y1 <= yb) { mn = min(mn, s.x1); mx = max(mx, s.x1); }  // left chain at / towards its corner row
+    return mn <= x_hi && mx >= x_lo;
+}
+
 // Stable insertion sort of 3 keys with strict < (Swift's sort on 3 elements, R:271).  Returns the permutation
 // as three 2-bit fields: perm = i0 | i1<<2 | i2<<4.
 __device__ __forceinline__ unsigned sort3_perm(float ya, float yb, float yc) {

@@ -37,3 +37,47 @@ def test_random_and_adversarial():
         kk = (2 ** 31 - 1) // small
         check(kk * small, small)
         check(kk * small - 1, small)
+
+
+def test_rect_touched_never_drops_a_covered_tile():
+    """csrc/sr_math.cuh::rect_touched (bbox-tile pruning in k_setup) restated with Python ints: for random integer
+    triangles, including flat tops/bottoms, slivers and repeated corners, a tile that holds a covered pixel of the
+    span rule (Renderer.swift:275-283, 467-494) is never rejected; and the test does prune something."""
+    from oracle import literal_py as P
+    rng = np.random.default_rng(11)
+    T, W, H = 16, 200, 160
+    kept = pruned = 0
+    for trial in range(3000):
+        k = trial % 6
+        pts = rng.integers(-40, 240, size=(3, 2))
+        if k == 1:
+            pts[1, 1] = pts[2, 1]                       # two corners on one row
+        elif k == 2:
+            pts[0, 1] = pts[1, 1] = pts[2, 1]           # all on one row
+        elif k == 3:
+            pts[1] = pts[0]                             # repeated corner
+        elif k == 4:
+            pts[:, 0] = pts[0, 0] + rng.integers(-2, 3, size=3)   # sliver
+        order = sorted(range(3), key=lambda q: pts[q][1])       # stable, like R:271
+        s = [(int(pts[q][0]), int(pts[q][1])) for q in order]
+        y0, y1 = max(s[0][1], 0), min(s[2][1], H - 1)
+        xmin, xmax = max(min(p[0] for p in s), 0), min(max(p[0] for p in s), W - 1)
+        if y0 > y1 or xmin > xmax:
+            continue
+        spans = {}
+        for y in range(y0, y1 + 1):
+            a, b = P.interpolate(s, y), P.interpolate([s[0], s[2]], y)
+            spans[y] = (min(a, b), max(a, b))
+        for ty in range(y0 // T, y1 // T + 1):
+            for tx in range(xmin // T, xmax // T + 1):
+                ya, yb = max(ty * T, s[0][1], 0), min(ty * T + T - 1, s[2][1], H - 1)
+                x_lo, x_hi = tx * T, min(tx * T + T - 1, W - 1)
+                covered = any(spans[y][0] <= x_hi and spans[y][1] >= x_lo for y in range(ya, yb + 1))
+                mn, mx = min(spans[ya][0], spans[yb][0]), max(spans[ya][1], spans[yb][1])
+                if ya < s[1][1] <= yb:
+                    mn, mx = min(mn, s[1][0]), max(mx, s[1][0])
+                keep = mn <= x_hi and mx >= x_lo
+                assert keep or not covered, (s, tx, ty)
+                kept += keep
+                pruned += not keep
+    assert pruned > 0.2 * (kept + pruned)

@@ -212,7 +212,7 @@ def test_pair_buffer_regrow(env):
         for k in env:
             del os.environ[k]
     try:
-        v, i = random_tris(41, 700 if not env else 400, spread=1.5)
+        v, i = random_tris(41, 1000, spread=1.5)
         for dt in (False, True):
             c, d = gpu_render(r, v, i, I4, 1920, 1080, depth_test=dt)
             rc, rc_c, rc_d, _ = O.render(v, i, I4, 1920, 1080, flags=O.DEPTH_LESS if dt else 0)
