@@ -286,12 +286,19 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
             s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0, 0.0, 0.0, 0.0, 0.0};
         __syncwarp();
     }
-    // bbox tile (tx, ty) of staged triangle `src`: can it hold a covered pixel?  (prunes the corners of the bbox)
-    auto tile_touched = [&](int src, int tx, int ty) -> bool {
+    // tile row `ty` of staged triangle `src`: the tile columns [ta, tb] that can hold a covered pixel (prunes the
+    // corners of the bbox; one evaluation serves the whole tile row)
+    auto tile_row_range = [&](int src, const StagedRect& r, int ty, int& ta, int& tb) {
+        ta = r.tx0;
+        tb = r.tx0 + (r.w & 0x7fff) - 1;
+        if (!(r.w & 0x8000)) return;
         const StagedTri t = s_tri[wbase + src];
         const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
         const int ya = max(max(ty * TILE, t.y0), 0), yb = min(min(ty * TILE + TILE - 1, t.y2), fp.height - 1);
-        return rect_touched(st, EdgeRcp{t.r01, t.r12, t.r02}, tx * TILE, min(tx * TILE + TILE - 1, fp.width - 1), ya, yb);
+        int mn, mx;
+        row_band_extent(st, EdgeRcp{t.r01, t.r12, t.r02}, ya, yb, mn, mx);
+        ta = max(ta, mn >> TILE_SHIFT);
+        tb = min(tb, mx >> TILE_SHIFT);
     };
     if (binning) {
         // slab lists: the record of triangle `prim` lives at recs[prim - batch start] (nothing waits for the counter);
@@ -307,63 +314,39 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
         const int items = large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0;
         s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (items > 2 ? 0x8000 : 0) | (cslot << 16), (int)slot};
         __syncwarp();
-        // (a) large triangles: one item per bbox tile.
+        // (a) large triangles: one item per bbox tile ROW, re-balanced over the warp; the item walks the touched tiles.
         //   compact lists: counts[tile][chunk]++ here, k_scan + k_bin_fill build the lists afterwards
         //   slab lists   : the returned count IS the position inside the fixed-capacity segment of (tile, chunk);
-        //                  four atomics per lane are in flight before the first dependent store
-        if (!fp.slab_cap) {
-            warp_balance(items, [&](int src, int item) {
-                const StagedRect r = s_rect[wbase + src];
-                const int w = r.w & 0x7fff, cs = r.w >> 16;
-                int qy, qx;
-                divmod_tiles(item, w, qy, qx);
-                const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
-                if (fp.batched && tile_done[tile] == fp.epoch) return;
-                if ((r.w & 0x8000) && !tile_touched(src, r.tx0 + qx, r.ty0 + qy)) return;
-                atomicAdd(&counts[(size_t)tile * NCHUNK + cs], 1u);
-            });
-        } else {
-            int incl = items;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (unsigned)d) incl += t; }
-            const int excl = incl - items;
-            const int total = __shfl_sync(0xffffffffu, incl, 31);
-            unsigned seg_max = 0;
-            for (int b0 = 0; b0 < total; b0 += 128) {
-                unsigned pos[4], seg[4], val[4];
+        //                  up to four atomics per lane are in flight before the first dependent store
+        unsigned seg_max = 0;
+        warp_balance(large ? (ty1 - ty0 + 1) : 0, [&](int src, int item) {
+            const StagedRect r = s_rect[wbase + src];
+            const int cs = r.w >> 16, ty = r.ty0 + item;
+            int ta, tb;
+            tile_row_range(src, r, ty, ta, tb);
+            const unsigned seg0 = (unsigned)(ty * fp.tiles_x) * NCHUNK + cs;
+            if (!fp.slab_cap) {
+                for (int tx = ta; tx <= tb; ++tx)
+                    if (!(fp.batched && tile_done[ty * fp.tiles_x + tx] == fp.epoch)) atomicAdd(&counts[seg0 + tx * NCHUNK], 1u);
+                return;
+            }
+            for (int tx = ta; tx <= tb; tx += 4) {
+                unsigned pos[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const int k = b0 + u * 32 + (int)lane;
-                    int j = 0;
-#pragma unroll
-                    for (int step = 16; step > 0; step >>= 1) {
-                        const int e = __shfl_sync(0xffffffffu, excl, j + step);
-                        if (e <= k) j += step;
-                    }
-                    const int ej = __shfl_sync(0xffffffffu, excl, j);
                     pos[u] = 0xffffffffu;
-                    if (k < total) {
-                        const StagedRect r = s_rect[wbase + j];
-                        const int item = k - ej, w = r.w & 0x7fff, cs = r.w >> 16;
-                        int qy, qx;
-                        divmod_tiles(item, w, qy, qx);
-                        const int tile = (r.ty0 + qy) * fp.tiles_x + r.tx0 + qx;
-                        val[u] = (unsigned)r.slot;
-                        seg[u] = (unsigned)tile * NCHUNK + cs;
-                        if (!(fp.batched && tile_done[tile] == fp.epoch) &&
-                            (!(r.w & 0x8000) || tile_touched(j, r.tx0 + qx, r.ty0 + qy)))
-                            pos[u] = atomicAdd(&counts[seg[u]], 1u);
-                    }
+                    if (tx + u <= tb && !(fp.batched && tile_done[ty * fp.tiles_x + tx + u] == fp.epoch))
+                        pos[u] = atomicAdd(&counts[seg0 + (tx + u) * NCHUNK], 1u);
                 }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (pos[u] == 0xffffffffu) continue;
-                    if (pos[u] < (unsigned)fp.slab_cap) pairs[(size_t)seg[u] * fp.slab_cap + pos[u]] = val[u];
+                    if (pos[u] < (unsigned)fp.slab_cap) pairs[(size_t)(seg0 + (tx + u) * NCHUNK) * fp.slab_cap + pos[u]] = (unsigned)r.slot;
                     else seg_max = max(seg_max, pos[u] + 1u);
                 }
             }
-            if (seg_max) atomicMax(&status->seg_max, seg_max);      // a segment overflowed: the host grows the slabs and re-runs
-        }
+        });
+        if (seg_max) atomicMax(&status->seg_max, seg_max);          // a segment overflowed: the host grows the slabs and re-runs
     }
 
     // (b) small triangles: one item per clipped row -> global atomics on the visibility words

@@ -108,12 +108,17 @@ __device__ __forceinline__ void span_row_rcp(const SortedTri& s, const EdgeRcp& 
 // its last row, R:470-471), so over the rows ya..yb the smallest left end / largest right end are reached at ya, yb,
 // or are bounded by s1.x when the middle corner's row lies in (ya, yb].  The test "min end <= x_hi and max end >= x_lo" never rejects
 // a rectangle that holds a covered pixel; it may keep one that holds none (the two extremes can sit on different rows).
-__device__ __forceinline__ bool rect_touched(const SortedTri& s, const EdgeRcp& m, int x_lo, int x_hi, int ya, int yb) {
+__device__ __forceinline__ void row_band_extent(const SortedTri& s, const EdgeRcp& m, int ya, int yb, int& mn, int& mx) {
     int l0, r0, l1, r1;
     span_row_rcp(s, m, ya, l0, r0);
     span_row_rcp(s, m, yb, l1, r1);
-    int mn = min(l0, l1), mx = max(r0, r1);
+    mn = min(l0, l1);
+    mx = max(r0, r1);
     if (s.y1 > ya && s.y1 <= yb) { mn = min(mn, s.x1); mx = max(mx, s.x1); }  // left chain at / towards its corner row
+}
+__device__ __forceinline__ bool rect_touched(const SortedTri& s, const EdgeRcp& m, int x_lo, int x_hi, int ya, int yb) {
+    int mn, mx;
+    row_band_extent(s, m, ya, yb, mn, mx);
     return mn <= x_hi && mx >= x_lo;
 }
 
