@@ -15,7 +15,7 @@ using namespace sr;
 namespace {
 
 constexpr int MAX_PROF = 64;
-constexpr size_t kSlabLimit = 4ull << 30;
+constexpr size_t kSlabLimit = 8ull << 30;
 
 template <class T>
 struct DevBuf {
@@ -49,7 +49,9 @@ struct sr_ctx {
 
     // per-frame working set
     DevBuf<float4> sv;                      // screen-space vertices (sx, sy, z, 0)
-    DevBuf<TriRec> recs;                    // bin list
+    DevBuf<TriRec> recs;                    // bin list (compact lists only)
+    DevBuf<float4> ztri;                    // depth mode: corner depths of binned triangles
+    DevBuf<TriRec> slab;                    // slab lists: ntiles x NCHUNK segments of slab_cap records
     DevBuf<unsigned> counts, cursor;        // (tile, chunk) counters / list cursors
     DevBuf<unsigned> pairs;                 // tile lists
     DevBuf<unsigned> vis32;                 // depth-off visibility words (prim+1), self-clearing
@@ -152,15 +154,21 @@ void launch_pdl(sr_ctx* c, void (*kernel)(KArgs...), unsigned grid, unsigned blo
 
 int primitive_vertices(int prim) { return prim == SR_LINE ? 2 : 3; }   // R:179-188
 
+// Buffers of the compact-list fallback: one record per triangle and the pair array (grown on demand by re-runs).
+int ensure_compact(sr_ctx* c) {
+    const size_t ntris = c->nidx / 3;
+    SR_CUDA(c, c->recs.reserve(std::max<size_t>(ntris, 1)));
+    if (!c->pairs.p) SR_CUDA(c, c->pairs.reserve(std::min<size_t>(std::max<size_t>(4 * ntris, 1u << 20), 64u << 20)));
+    return SR_OK;
+}
+
 // Make sure the per-frame buffers fit this mesh and resolution.  Newly allocated self-clearing buffers are put
 // into their cleared state here; afterwards the kernels keep them clean.
 int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews, cudaStream_t st) {
     const size_t npx = (size_t)W * H;
     const size_t tiles = (size_t)div_up(W, TILE) * div_up(H, TILE);
     const size_t ncnt = tiles * NCHUNK;
-    const size_t ntris = c->nidx / 3;
     SR_CUDA(c, c->sv.reserve(std::max<size_t>(c->nverts, 1)));
-    SR_CUDA(c, c->recs.reserve(std::max<size_t>(ntris, 1)));
     if (ncnt > c->counts.cap) {
         SR_CUDA(c, c->counts.reserve(ncnt));
         SR_CUDA(c, cudaMemsetAsync(c->counts.p, 0, ncnt * sizeof(unsigned), st));
@@ -182,16 +190,14 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
         SR_CUDA(c, cudaMemsetAsync(c->ticket.p, 0, sizeof(unsigned), st));
         c->ticket_base = 0;
     }
-    if (!c->pairs.p) {
-        size_t want = std::min<size_t>(std::max<size_t>(4 * ntris, 1u << 20), 64u << 20);
-        SR_CUDA(c, c->pairs.reserve(want));
-    }
     if (c->slab_mode) {
         const size_t need = ncnt * c->slab_cap;
-        if (need * sizeof(unsigned) > kSlabLimit) c->slab_mode = false;
-        else SR_CUDA(c, c->pairs.reserve(need));
+        if (need * sizeof(TriRec) > kSlabLimit) c->slab_mode = false;
+        else SR_CUDA(c, c->slab.reserve(need));
     }
+    if (!c->slab_mode) { int rc = ensure_compact(c); if (rc) return rc; }
     if (depth_mode) {
+        SR_CUDA(c, c->ztri.reserve(std::max<size_t>(c->nidx / 3, 1)));
         if (npx > c->vis64.cap) {
             SR_CUDA(c, c->vis64.reserve(npx));
             k_fill_u64<<<div_up(npx, 256), 256, 0, st>>>(c->vis64.p, npx, SR_KEY_EMPTY);
@@ -238,7 +244,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
         fp.epoch = ++c->frame_epoch;
         fp.batched = (!depth_mode && c->batched_mode && ntris >= (1 << 16)) ? 1 : 0;
-        fp.slab_cap = (c->slab_mode && (size_t)fp.ntiles * NCHUNK * c->slab_cap <= c->pairs.cap) ? (int)c->slab_cap : 0;
+        fp.slab_cap = (c->slab_mode && (size_t)fp.ntiles * NCHUNK * c->slab_cap <= c->slab.cap) ? (int)c->slab_cap : 0;
         c->call_slab_cap = (unsigned)fp.slab_cap;
         c->last_ntiles = (size_t)fp.ntiles;
         fp.nobin = (c->nobin_mode && c->allow_nobin && !fp.batched) ? 1 : 0;
@@ -254,7 +260,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         } else {
             batches[nb++] = BatchParams{0, ntris, 0, 0, 1};
         }
-        ShadeIn in{c->idx.p, c->sv.p, c->col.p};
+        ShadeIn in{c->idx.p, c->sv.p, c->col.p, c->ztri.p};
         for (int b = 0; b < nb; ++b) {
             BatchParams& bp = batches[b];
             const int n = bp.hi - bp.lo;
@@ -263,7 +269,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 prof_mark(c, st, "k_setup");
                 auto ks = depth_mode ? (fp.nobin ? k_setup<true, false> : k_setup<true, true>)
                                      : (fp.nobin ? k_setup<false, false> : k_setup<false, true>);
-                launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->pairs.p, c->tile_done.p, d_status);
+                launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             if (!fp.nobin && !fp.slab_cap) {
@@ -283,8 +289,9 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             prof_mark(c, st, "k_tile");
             // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
             const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;
-            if (depth_mode) launch_pdl(c, k_tile<true>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
-            else            launch_pdl(c, k_tile<false>, tgrid, 256, st, fp, bp, in, c->recs.p, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            const TriRec* tile_recs = fp.slab_cap ? c->slab.p : c->recs.p;
+            if (depth_mode) launch_pdl(c, k_tile<true>, tgrid, 256, st, fp, bp, in, tile_recs, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            else            launch_pdl(c, k_tile<false>, tgrid, 256, st, fp, bp, in, tile_recs, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
             c->launches++;
         }
     } else {
@@ -344,8 +351,15 @@ int collect_status(sr_ctx* c, size_t nviews, cudaStream_t st, std::vector<size_t
             unsigned cap = c->slab_cap;
             while (cap < seg + seg / 4) cap *= 2;
             c->stats.bin_regrows++;
-            if (c->last_ntiles * NCHUNK * (size_t)cap * sizeof(unsigned) > kSlabLimit) c->slab_mode = false;
-            else { c->slab_cap = cap; SR_CUDA(c, c->pairs.reserve(c->last_ntiles * NCHUNK * (size_t)cap)); }
+            if (c->last_ntiles * NCHUNK * (size_t)cap * sizeof(TriRec) > kSlabLimit) {
+                c->slab_mode = false;
+                c->slab.release();
+                int rc = ensure_compact(c);
+                if (rc) return rc;
+            } else {
+                c->slab_cap = cap;
+                SR_CUDA(c, c->slab.reserve(c->last_ntiles * NCHUNK * (size_t)cap));
+            }
         }
     }
     if (c->call_nobin && !rerun->empty()) c->nobin_mode = false;
@@ -460,7 +474,7 @@ void sr_destroy(sr_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
-    c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release();
+    c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release(); c->slab.release(); c->ztri.release();
     c->counts.release(); c->cursor.release(); c->pairs.release(); c->vis32.release(); c->vis64.release();
     c->look.release(); c->ticket.release(); c->status.release(); c->tile_done.release();
     for (int i = 0; i < 2; ++i) {

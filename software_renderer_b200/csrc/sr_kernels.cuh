@@ -48,14 +48,14 @@ struct ViewStatus {
     unsigned open_after_first;          // batched mode: tiles still open after the first batch
 };
 
-// Bin-list record of a large triangle (64 B): corners SORTED as R:271 leaves them, the sort permutation (to get
-// back to the original a,b,c order of R:251 for the depth mode), and the three per-edge reciprocals of sr_math.cuh.
-struct __align__(16) TriRec {
+// Bin-list record of a large triangle (32 B = one sector): corners SORTED as R:271 leaves them and the sort
+// permutation (to get back to the original a,b,c order of R:251).  Slab lists hold the records themselves (the tile
+// kernel reads them with no indirection); compact lists hold indices into `recs`.  Depth mode keeps the three
+// corner depths (original order) in a side array indexed by primitive, ztri[prim].
+struct __align__(32) TriRec {
     int x0, y0, x1, y1, x2, y2;
     unsigned prim;
     unsigned perm;                       // sorted position k holds original corner (perm >> 2k) & 3
-    double r01, r12, r02;                // edge_rcp(y1-y0), (y2-y1), (y2-y0)
-    unsigned long long _pad;
 };
 
 __device__ __forceinline__ SortedTri sort_corners(int ax, int ay, int bx, int by, int cx, int cy, unsigned perm) {
@@ -169,7 +169,7 @@ __device__ __forceinline__ void divmod_tiles(int item, int w, int& q, int& r) {
     if (r < 0) { --q; r += w; } else if (r >= w) { ++q; r -= w; }
 }
 
-struct __align__(16) StagedTri { int x0, y0, x1, y1, x2, y2; unsigned prim; int ystart; double r01, r12, r02; double _pad; };   // sorted corners + edge reciprocals
+struct __align__(16) StagedTri { int x0, y0, x1, y1, x2, y2; unsigned prim; int ystart; double r01, r12, r02; unsigned perm; unsigned _pad; };   // sorted corners, edge reciprocals, permutation
 struct __align__(16) StagedRect { int tx0, ty0, w, slot; };                                   // tile rectangle; w | cslot<<16
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -182,8 +182,8 @@ template <bool DEPTH, bool BIN>
 __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, const float4* __restrict__ sv, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
-                                               unsigned* __restrict__ counts, unsigned* __restrict__ pairs,
-                                               const unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
+                                               unsigned* __restrict__ counts, TriRec* __restrict__ slab,
+                                               float4* __restrict__ ztri, const unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
     pdl_wait();
     __shared__ StagedTri s_tri[256];
     __shared__ StagedRect s_rect[BIN ? 256 : 1];
@@ -203,6 +203,7 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     SortedTri s = {};
     int ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, y0 = 0, y1 = -1, xmin = 0, xmax = -1;
     unsigned perm = 0;
+    float za = 0.0f, zb = 0.0f, zc = 0.0f;
     if (valid) {
         const int i0 = idx[3 * (size_t)prim], i1 = idx[3 * (size_t)prim + 1], i2 = idx[3 * (size_t)prim + 2];
         const float4 a = sv[i0], b = sv[i1], c = sv[i2];
@@ -210,6 +211,7 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
             skipped = true;                                         // the reference traps here (R:251, R:271)
         } else {
             perm = sort3_perm(a.y, b.y, c.y);                       // R:271 float keys, strict <, stable
+            za = a.z; zb = b.z; zc = c.z;
             ax = __float2int_rz(a.x); ay = __float2int_rz(a.y);     // simd_long2(...) truncates toward zero
             bx = __float2int_rz(b.x); by = __float2int_rz(b.y);
             cx = __float2int_rz(c.x); cy = __float2int_rz(c.y);
@@ -281,9 +283,9 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
         // division-free shortcuts of span_row
         if (large && binning)
             s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0,
-                                           edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), 0.0};
+                                           edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), perm, 0u};
         else if (small)
-            s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0, 0.0, 0.0, 0.0, 0.0};
+            s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0, 0.0, 0.0, 0.0, perm, 0u};
         __syncwarp();
     }
     // tile row `ty` of staged triangle `src`: the tile columns [ta, tb] that can hold a covered pixel (prunes the
@@ -301,13 +303,12 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
         tb = min(tb, mx >> TILE_SHIFT);
     };
     if (binning) {
-        // slab lists: the record of triangle `prim` lives at recs[prim - batch start] (nothing waits for the counter);
-        // compact lists: records are compacted, k_bin_fill walks them
-        unsigned slot = (unsigned)(prim - bp.lo);
-        if (!fp.slab_cap) slot = __shfl_sync(0xffffffffu, base, 0) + __popc(m_large & ((1u << lane) - 1u));
-        if (large) {
-            const StagedTri& t = s_tri[threadIdx.x];
-            recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm, t.r01, t.r12, t.r02, 0ull};
+        // compact lists: records are compacted into `recs`, the lists hold their slots; slab lists hold records
+        unsigned slot = 0;
+        if (DEPTH && large) ztri[prim] = make_float4(za, zb, zc, 0.0f);
+        if (!fp.slab_cap) {
+            slot = __shfl_sync(0xffffffffu, base, 0) + __popc(m_large & ((1u << lane) - 1u));
+            if (large) recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm};
         }
         // chunks are stored in DESCENDING index order inside each tile list
         const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
@@ -341,8 +342,13 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (pos[u] == 0xffffffffu) continue;
-                    if (pos[u] < (unsigned)fp.slab_cap) pairs[(size_t)(seg0 + (tx + u) * NCHUNK) * fp.slab_cap + pos[u]] = (unsigned)r.slot;
-                    else seg_max = max(seg_max, pos[u] + 1u);
+                    if (pos[u] < (unsigned)fp.slab_cap) {
+                        const StagedTri& t = s_tri[wbase + src];
+                        slab[(size_t)(seg0 + (tx + u) * NCHUNK) * fp.slab_cap + pos[u]] =
+                            TriRec{t.x0, t.y0, t.x1, t.y1, t.x2, t.y2, t.prim, t.perm};
+                    } else {
+                        seg_max = max(seg_max, pos[u] + 1u);
+                    }
                 }
             }
         });
@@ -523,7 +529,8 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
                         const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                         const int tx = r.tx0 + qx, ty = r.ty0 + qy;
                         const int ya = max(max(ty * TILE, t.y0), 0), yb = min(min(ty * TILE + TILE - 1, t.y2), fp.height - 1);
-                        keep = rect_touched(st, EdgeRcp{t.r01, t.r12, t.r02}, tx * TILE, min(tx * TILE + TILE - 1, fp.width - 1), ya, yb);
+                        keep = rect_touched(st, EdgeRcp{edge_rcp(t.y1 - t.y0), edge_rcp(t.y2 - t.y1), edge_rcp(t.y2 - t.y0)},
+                                            tx * TILE, min(tx * TILE + TILE - 1, fp.width - 1), ya, yb);
                     }
                     if (keep)
                         pos[u] = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);
@@ -555,6 +562,7 @@ struct ShadeIn {
     const int* idx;
     const float4* sv;
     const float4* col;
+    const float4* ztri;     // depth mode: corner depths of binned triangles, by primitive
 };
 
 __device__ __forceinline__ void shade_pixel(const ShadeIn& in, unsigned prim, int x, int y, bool depth_mode,
@@ -579,6 +587,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     __shared__ __align__(16) unsigned short s_mask[TILE][TILE_BATCH];
     __shared__ unsigned s_prim[TILE_BATCH];
     __shared__ TriRec s_rec[2][TILE_BATCH];
+    __shared__ double s_rcp[TILE_BATCH][3];                 // per-edge reciprocals of the current round's triangles
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
     __shared__ unsigned s_off[NCHUNK + 1];                 // slab lists: prefix of the tile's 16 segment lengths
@@ -586,22 +595,26 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
     const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
-    if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;
+    const bool late = fp.batched && bp.index > 0;                   // only later batches can meet retired tiles
+    if (late && status->tiles_done >= (unsigned)fp.ntiles) return;
 
     // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA launches
     for (int tile = blockIdx.x; tile < fp.ntiles; tile += gridDim.x) {
-    if (fp.batched && tile_done[tile] == fp.epoch) continue;        // retired by an earlier batch
+    if (late && tile_done[tile] == fp.epoch) continue;              // retired by an earlier batch
     const int tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
     const int x = tx * TILE + px, y = ty * TILE + py;
     const bool inside = x < fp.width && y < fp.height;
     const size_t o = (size_t)y * fp.width + x;
 
+    // visibility words left by the direct path (or parked by an earlier batch); re-armed after the loop
     unsigned v = 0;
     unsigned long long k = SR_KEY_EMPTY;
     if (inside) {
-        if (DEPTH) { k = vis64[o]; if (k != SR_KEY_EMPTY) vis64[o] = SR_KEY_EMPTY; }
-        else       { v = vis32[o]; if (v) vis32[o] = 0u; }
+        if (DEPTH) k = vis64[o];
+        else       v = vis32[o];
     }
+    const unsigned v_in = v;
+    const unsigned long long k_in = k;
 
     const size_t seg = (size_t)tile * NCHUNK;
     const bool slab = fp.slab_cap > 0 && !fp.nobin;
@@ -634,33 +647,38 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         if (tid == 0 && end) atomicAdd(&status->total_pairs[bp.index], end);
     }
     unsigned p = begin;
-    auto pair_at = [&](unsigned q) -> unsigned {
-        if (!slab) return pairs[q];
-        int c = 0;
-#pragma unroll
-        for (int step = NCHUNK / 2; step > 0; step >>= 1) if (s_off[c + step] <= q) c += step;
-        return pairs[(seg + c) * (size_t)fp.slab_cap + (q - s_off[c])];
-    };
 
-    // software pipeline: records of the NEXT batch travel global -> shared with cp.async (no registers held) while
-    // the current batch is processed; the slot indices are fetched one batch further ahead.
-    auto fetch = [&](int buf, unsigned slot) {
-        if (row < 4) __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][j]) + 16 * row,
-                                             reinterpret_cast<const char*>(recs + slot) + 16 * row, 16);
+    // software pipeline: the records of the NEXT round travel global -> shared with cp.async (no registers held)
+    // while the current round is processed.  Two threads per triangle move 16 B each.
+    auto fetch = [&](int buf, unsigned q) {
+        const TriRec* src;
+        if (slab) {
+            int c = 0;
+#pragma unroll
+            for (int step = NCHUNK / 2; step > 0; step >>= 1) if (s_off[c + step] <= q) c += step;
+            src = recs + (seg + c) * (size_t)fp.slab_cap + (q - s_off[c]);
+        } else {
+            src = recs + pairs[q];
+        }
+        __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][j]) + 16 * row,
+                                reinterpret_cast<const char*>(src) + 16 * row, 16);
     };
-    unsigned slot_next = 0;
-    if (p + j < end && row < 4) fetch(0, pair_at(p + j));
+    if (p + j < end && row < 2) fetch(0, p + j);
     __pipeline_commit();
-    if (p + TILE_BATCH + j < end && row < 4) slot_next = pair_at(p + TILE_BATCH + j);
     int cur = 0;
     __pipeline_wait_prior(0);
     __syncthreads();                                       // s_rec[0] complete
 
     while (p < end) {
         const int n = min((unsigned)TILE_BATCH, end - p);
-        if (p + TILE_BATCH + j < end) fetch(cur ^ 1, slot_next);
+        if (p + TILE_BATCH + j < end && row < 2) fetch(cur ^ 1, p + TILE_BATCH + j);
         __pipeline_commit();
-        if (p + 2 * TILE_BATCH + j < end && row < 4) slot_next = pair_at(p + 2 * TILE_BATCH + j);
+        // per-edge reciprocals of this round's triangles: rows 0..2 of a triangle's 16 lanes compute one each
+        if (j < n && row < 3) {
+            const TriRec& t = s_rec[cur][j];
+            s_rcp[j][row] = edge_rcp(row == 0 ? t.y1 - t.y0 : (row == 1 ? t.y2 - t.y1 : t.y2 - t.y0));
+        }
+        __syncwarp();
         {   // phase A: (triangle j, row) -> column mask
             unsigned mask = 0;
             if (j < n) {
@@ -668,7 +686,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                 const SortedTri s = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                 if (yy >= s.y0 && yy <= s.y2 && yy < fp.height) {
                     int l, r;
-                    span_row_rcp(s, EdgeRcp{t.r01, t.r12, t.r02}, yy, l, r);
+                    span_row_rcp(s, EdgeRcp{s_rcp[j][0], s_rcp[j][1], s_rcp[j][2]}, yy, l, r);
                     l = max(l, x_lo);
                     r = min(r, x_hi);
                     if (l <= r) mask = ((2u << (r - l)) - 1u) << (l - x_lo);
@@ -679,8 +697,8 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                         int oc[6];
                         unsort_corners(t, oc);
                         s_bt[j] = bary_setup(oc[0], oc[1], oc[2], oc[3], oc[4], oc[5]);
-                        const int i0 = in.idx[3 * (size_t)t.prim], i1 = in.idx[3 * (size_t)t.prim + 1], i2 = in.idx[3 * (size_t)t.prim + 2];
-                        s_z[j][0] = in.sv[i0].z; s_z[j][1] = in.sv[i1].z; s_z[j][2] = in.sv[i2].z;
+                        const float4 z = in.ztri[t.prim];
+                        s_z[j][0] = z.x; s_z[j][1] = z.y; s_z[j][2] = z.z;
                     }
                 }
             }
@@ -730,7 +748,9 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         if (shade_now && tid == 0) { tile_done[tile] = fp.epoch; atomicAdd(&status->tiles_done, 1u); }
     }
     if (!inside) continue;
-    if (!shade_now) { if (v) vis32[o] = v; continue; }   // park for the next batch
+    if (!shade_now) { if (v != v_in) vis32[o] = v; continue; }      // park for the next batch
+    if (DEPTH) { if (k_in != SR_KEY_EMPTY) vis64[o] = SR_KEY_EMPTY; }   // re-arm the visibility word for the next frame
+    else       { if (v_in) vis32[o] = 0u; }
     unsigned bgra = 0u;                                  // clear colour (R:205)
     float depth = __int_as_float(0x7f800000);            // +inf (R:206)
     if (DEPTH) { if (k != SR_KEY_EMPTY) shade_pixel(in, (unsigned)k, x, y, true, bgra, depth); }
