@@ -601,7 +601,8 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA launches
     for (int tile = blockIdx.x; tile < fp.ntiles; tile += gridDim.x) {
     if (late && tile_done[tile] == fp.epoch) continue;              // retired by an earlier batch
-    const int tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
+    int tx, ty;
+    divmod_tiles(tile, fp.tiles_x, ty, tx);
     const int x = tx * TILE + px, y = ty * TILE + py;
     const bool inside = x < fp.width && y < fp.height;
     const size_t o = (size_t)y * fp.width + x;
@@ -648,9 +649,10 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     }
     unsigned p = begin;
 
-    // software pipeline: the records of the NEXT round travel global -> shared with cp.async (no registers held)
-    // while the current round is processed.  Two threads per triangle move 16 B each.
-    auto fetch = [&](int buf, unsigned q) {
+    // software pipeline run by warp 0: lanes 0..15 bring the records of the NEXT round global -> shared with cp.async
+    // (no registers held) while the current round is processed; the block barrier that ends the round publishes them.
+    const bool producer = tid < 32;
+    auto fetch = [&](int buf, unsigned q) {                // lanes 0..15 of warp 0, q = list position of triangle `tid`
         const TriRec* src;
         if (slab) {
             int c = 0;
@@ -660,19 +662,23 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         } else {
             src = recs + pairs[q];
         }
-        __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][j]) + 16 * row,
-                                reinterpret_cast<const char*>(src) + 16 * row, 16);
+        __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][tid]), reinterpret_cast<const char*>(src), 16);
+        __pipeline_memcpy_async(reinterpret_cast<char*>(&s_rec[buf][tid]) + 16, reinterpret_cast<const char*>(src) + 16, 16);
     };
-    if (p + j < end && row < 2) fetch(0, p + j);
-    __pipeline_commit();
+    if (producer) {
+        if (tid < TILE_BATCH && p + tid < end) fetch(0, p + tid);
+        __pipeline_commit();
+        __pipeline_wait_prior(0);
+    }
     int cur = 0;
-    __pipeline_wait_prior(0);
     __syncthreads();                                       // s_rec[0] complete
 
     while (p < end) {
         const int n = min((unsigned)TILE_BATCH, end - p);
-        if (p + TILE_BATCH + j < end && row < 2) fetch(cur ^ 1, p + TILE_BATCH + j);
-        __pipeline_commit();
+        if (producer) {
+            if (tid < TILE_BATCH && p + TILE_BATCH + tid < end) fetch(cur ^ 1, p + TILE_BATCH + tid);
+            __pipeline_commit();
+        }
         // per-edge reciprocals of this round's triangles: rows 0..2 of a triangle's 16 lanes compute one each
         if (j < n && row < 3) {
             const TriRec& t = s_rec[cur][j];
@@ -728,7 +734,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         }
         p += n;
         cur ^= 1;
-        __pipeline_wait_prior(0);                          // next records landed (made visible by the barrier below)
+        if (producer) __pipeline_wait_prior(0);            // next records landed (made visible by the barrier below)
         if (DEPTH) {
             __syncthreads();
         } else {
