@@ -230,7 +230,9 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
     unsigned* color32 = reinterpret_cast<unsigned*>(color_dev);
     c->prof_n = 0;
 
-    if (prim != SR_LINE && nverts > 0) {
+    // batched frames (depth off, heavy overdraw) transform corners inside k_setup, batch by batch
+    const bool batched_frame = prim == SR_TRIANGLE && !depth_mode && c->batched_mode && (c->nidx / 3) >= (1u << 16);
+    if (prim != SR_LINE && nverts > 0 && !batched_frame) {
         prof_mark(c, st, "k_transform");
         launch_pdl(c, k_transform, div_up(nverts, 256), 256, st, c->pos.p, nverts, M, (float)W, (float)H, c->sv.p);
         c->launches++;
@@ -243,7 +245,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.ntiles = fp.tiles_x * fp.tiles_y;
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
         fp.epoch = ++c->frame_epoch;
-        fp.batched = (!depth_mode && c->batched_mode && ntris >= (1 << 16)) ? 1 : 0;
+        fp.batched = batched_frame ? 1 : 0;
         fp.slab_cap = (c->slab_mode && (size_t)fp.ntiles * NCHUNK * c->slab_cap <= c->slab.cap) ? (int)c->slab_cap : 0;
         c->call_slab_cap = (unsigned)fp.slab_cap;
         c->last_ntiles = (size_t)fp.ntiles;
@@ -267,9 +269,11 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             while (n > 0 && ((n - 1) >> bp.chunk_shift) >= NCHUNK) bp.chunk_shift++;
             if (n > 0) {
                 prof_mark(c, st, "k_setup");
-                auto ks = depth_mode ? (fp.nobin ? k_setup<true, false> : k_setup<true, true>)
-                                     : (fp.nobin ? k_setup<false, false> : k_setup<false, true>);
-                launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
+                auto ks = depth_mode ? (fp.nobin ? k_setup<true, false, false> : k_setup<true, true, false>)
+                                     : (fp.nobin ? k_setup<false, false, false>
+                                                 : (fp.batched ? k_setup<false, true, true> : k_setup<false, true, false>));
+                XformIn xf{c->pos.p, M, (float)W, (float)H};
+                launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             if (!fp.nobin && !fp.slab_cap) {

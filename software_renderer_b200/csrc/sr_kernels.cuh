@@ -178,8 +178,16 @@ struct __align__(16) StagedRect { int tx0, ty0, w, slot; };                     
 // the warp, so one big triangle does not serialize 31 idle lanes.
 // ---------------------------------------------------------------------------------------------------------------
 // BIN = false: the speculative no-binning frame (fp.nobin): the large-triangle code is compiled out.
-template <bool DEPTH, bool BIN>
-__global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, const float4* __restrict__ sv, FrameParams fp,
+// XFORM = true: batched frames transform the three corners here (Vertex.apply + convertedToScreen, R:159-172, the
+// same deterministic function k_transform evaluates) and publish them in sv[] for shading, so vertices of triangles
+// that no batch ever reaches are never transformed and k_transform is not launched.
+struct XformIn {
+    const float* pos;
+    Mat4 M;
+    float fw, fh;
+};
+template <bool DEPTH, bool BIN, bool XFORM>
+__global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
@@ -206,7 +214,18 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, cons
     float za = 0.0f, zb = 0.0f, zc = 0.0f;
     if (valid) {
         const int i0 = idx[3 * (size_t)prim], i1 = idx[3 * (size_t)prim + 1], i2 = idx[3 * (size_t)prim + 2];
-        const float4 a = sv[i0], b = sv[i1], c = sv[i2];
+        float4 a, b, c;
+        if (XFORM) {
+            auto corner = [&](int i) {
+                const float3 t = transform_to_screen(xf.M, xf.pos[3 * (size_t)i], xf.pos[3 * (size_t)i + 1], xf.pos[3 * (size_t)i + 2], xf.fw, xf.fh);
+                const float4 r = make_float4(t.x, t.y, t.z, 0.0f);
+                sv[i] = r;                                  // shared vertices: every writer stores the same bits
+                return r;
+            };
+            a = corner(i0); b = corner(i1); c = corner(i2);
+        } else {
+            a = sv[i0]; b = sv[i1]; c = sv[i2];
+        }
         if (!(in_domain(a.x) && in_domain(a.y) && in_domain(b.x) && in_domain(b.y) && in_domain(c.x) && in_domain(c.y))) {
             skipped = true;                                         // the reference traps here (R:251, R:271)
         } else {
