@@ -290,6 +290,14 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 launch_pdl(c, k_bin_fill, grid, 256, st, c->recs.p, d_status, fp, bp, c->cursor.p, c->pairs.p, c->tile_done.p);
                 c->launches++;
             }
+            if (fp.nobin) {
+                prof_mark(c, st, "k_resolve");
+                const bool wide = npx >= (4u << 20);       // four pixels per thread once that still fills the GPU
+                auto kr = depth_mode ? (wide ? k_resolve<true, 4> : k_resolve<true, 1>) : (wide ? k_resolve<false, 4> : k_resolve<false, 1>);
+                launch_pdl(c, kr, div_up(div_up(npx, wide ? 4 : 1), 256), 256, st, in, W, npx, c->vis32.p, c->vis64.p, color32, depth_dev);
+                c->launches++;
+                continue;
+            }
             prof_mark(c, st, "k_tile");
             // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
             const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;

@@ -786,6 +786,61 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// K5': resolve kernel of the no-binning frames (fp.nobin: every triangle went through the direct path, so the
+// visibility words are final).  One thread per four consecutive pixels: 16-B loads of the words, shade the winners
+// (R:251-268), 16-B stores of colour and depth (clear fused, R:205-206), words re-armed for the next frame.
+// ---------------------------------------------------------------------------------------------------------------
+template <bool DEPTH, int PPT>                              // PPT pixels per thread: 4 (large images) or 1 (enough threads)
+__global__ void __launch_bounds__(256) k_resolve(ShadeIn in, int W, size_t npx, unsigned* __restrict__ vis32,
+                                                 unsigned long long* __restrict__ vis64, unsigned* __restrict__ color_out,
+                                                 float* __restrict__ depth_out) {
+    pdl_wait();
+    const size_t o = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * PPT;
+    if (o >= npx) return;
+    const int cnt = PPT == 1 ? 1 : (int)min((size_t)4, npx - o);
+    unsigned win[4] = {0u, 0u, 0u, 0u};                     // prim + 1, 0 = background
+    if (cnt == 4) {
+        if (DEPTH) {
+            const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(vis64 + o), b = *reinterpret_cast<const ulonglong2*>(vis64 + o + 2);
+            const unsigned long long k[4] = {a.x, a.y, b.x, b.y};
+            bool any = false;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) if (k[q] != SR_KEY_EMPTY) { win[q] = (unsigned)k[q] + 1u; any = true; }
+            if (any) {
+                const ulonglong2 e = make_ulonglong2(SR_KEY_EMPTY, SR_KEY_EMPTY);
+                *reinterpret_cast<ulonglong2*>(vis64 + o) = e;
+                *reinterpret_cast<ulonglong2*>(vis64 + o + 2) = e;
+            }
+        } else {
+            const uint4 v = *reinterpret_cast<const uint4*>(vis32 + o);
+            win[0] = v.x; win[1] = v.y; win[2] = v.z; win[3] = v.w;
+            if (v.x | v.y | v.z | v.w) *reinterpret_cast<uint4*>(vis32 + o) = make_uint4(0u, 0u, 0u, 0u);
+        }
+    } else {
+        for (int q = 0; q < cnt; ++q) {
+            if (DEPTH) { const unsigned long long k = vis64[o + q]; if (k != SR_KEY_EMPTY) { win[q] = (unsigned)k + 1u; vis64[o + q] = SR_KEY_EMPTY; } }
+            else       { win[q] = vis32[o + q]; if (win[q]) vis32[o + q] = 0u; }
+        }
+    }
+    int y = (int)(o / (size_t)W), x = (int)(o - (size_t)y * W);
+    unsigned bgra[4];
+    float depth[4];
+#pragma unroll
+    for (int q = 0; q < PPT; ++q) {
+        bgra[q] = 0u;                                       // clear colour (R:205)
+        depth[q] = __int_as_float(0x7f800000);              // +inf (R:206)
+        if (win[q]) shade_pixel(in, win[q] - 1u, x, y, DEPTH, bgra[q], depth[q]);
+        if (++x == W) { x = 0; ++y; }
+    }
+    if (cnt == 4) {
+        *reinterpret_cast<uint4*>(color_out + o) = make_uint4(bgra[0], bgra[1], bgra[2], bgra[3]);
+        if (depth_out) *reinterpret_cast<float4*>(depth_out + o) = make_float4(depth[0], depth[1], depth[2], depth[3]);
+    } else {
+        for (int q = 0; q < cnt; ++q) { color_out[o + q] = bgra[q]; if (depth_out) depth_out[o + q] = depth[q]; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // PrimitiveType.vertices (R:295-302): every corner plots one pixel, the last corner in submission order wins.
 // k_points_resolve also serves PrimitiveType.line, which draws nothing (R:289-293): clear only.
 // ---------------------------------------------------------------------------------------------------------------

@@ -357,3 +357,20 @@ def test_tiny_triangle_path_all_shapes(renderer):
     # the same shapes hanging over the image border
     shift = np.eye(4, dtype=np.float32); shift[0, 3] = -1.0 + 1.0 / W; shift[1, 3] = 1.0 - 1.0 / H
     assert_same(renderer, v, i, shift, W, H)
+
+
+@pytest.mark.parametrize("size", [(641, 479), (33, 7), (2051, 2049), (2048, 2050)])
+@pytest.mark.parametrize("depth_test", [False, True])
+def test_resolve_kernel_odd_sizes(size, depth_test):
+    """The no-binning resolve kernel handles four pixels per thread: widths and pixel counts that are not multiples
+    of four, rows straddled by one thread's four pixels."""
+    W, H = size
+    r = srb.CudaRenderer(0)
+    try:
+        v, i = S.cube_sphere(60 if W < 1000 else 420)
+        m = (np.diag([0.5, 0.5, 1.0, 1.0]).astype(np.float32) @ S.app_transform(0.9)).astype(np.float32)
+        for k in range(3):                                # frame 0 full pipeline, frames 1.. speculative (k_resolve)
+            assert_same(r, v, i, m, W, H, depth_test=depth_test)
+            assert r.stats()["nobin_reruns"] == 0 and r.stats()["binned_tris"] == 0
+    finally:
+        r.close()
