@@ -72,6 +72,7 @@ typedef struct sr_stats {
     uint64_t bin_regrows;     /* times a frame was re-run because the pair buffer had to grow */
     uint64_t pairs_consumed;  /* pairs the tile kernel read before its exact early-out */
     uint64_t batches_run;     /* index-descending batches that still had open tiles (0 = single-batch frame) */
+    uint64_t depth_culled;    /* depth mode: tile-list records rejected by their depth bound or never read */
     uint64_t nobin_reruns;    /* frames launched without the binning kernels that met a large triangle and were re-run */
     uint64_t gpu_launches;    /* kernels launched by the call */
     float    gpu_ms;          /* device time of the call's kernels, CUDA events on the context's stream */

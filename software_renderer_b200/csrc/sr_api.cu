@@ -72,6 +72,7 @@ struct sr_ctx {
     // tile lists as fixed-capacity slabs (k_setup fills them directly; no k_scan / k_bin_fill).  A segment that
     // overflows makes the host double the capacity and re-run the frame; past kSlabLimit bytes the context falls
     // back to compact lists (scan + fill) for good.  SR_SLAB=0 forces compact lists.
+    float z_lo = 0.0f, z_hi = 1.0f;      // depth mode: range of the triangles' depth bounds seen last frame (chunk thresholds)
     bool slab_mode = true;
     unsigned slab_cap = 32, call_slab_cap = 0;
     size_t last_ntiles = 0;
@@ -118,6 +119,13 @@ namespace {
             return SR_ERR_CUDA;                                                                        \
         }                                                                                              \
     } while (0)
+
+float depth_unord_host(unsigned o) {
+    const unsigned u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+    float f;
+    std::memcpy(&f, &u, sizeof f);
+    return f;
+}
 
 int fail(sr_ctx* c, int code, const char* msg) {
     if (c) c->err = msg;
@@ -249,6 +257,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.slab_cap = (c->slab_mode && (size_t)fp.ntiles * NCHUNK * c->slab_cap <= c->slab.cap) ? (int)c->slab_cap : 0;
         c->call_slab_cap = (unsigned)fp.slab_cap;
         c->last_ntiles = (size_t)fp.ntiles;
+        for (int q = 0; q < NCHUNK - 1; ++q) fp.zthr[q] = c->z_lo + (c->z_hi - c->z_lo) * (float)(q + 1) / (float)NCHUNK;
+        for (int q = 1; q < NCHUNK - 1; ++q) fp.zthr[q] = std::max(fp.zthr[q], fp.zthr[q - 1]);      // ascending, whatever the rounding
         fp.nobin = (c->nobin_mode && c->allow_nobin && !fp.batched) ? 1 : 0;
         if (fp.nobin) c->call_nobin = true;
         const int ncnt = fp.ntiles * NCHUNK;
@@ -394,6 +404,7 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
         c->stats.small_tris += s.n_small;
         for (int b = 0; b < MAX_BATCHES; ++b) { c->stats.binned_tris += s.n_large[b]; c->stats.tile_pairs += s.total_pairs[b]; }
         c->stats.pairs_consumed += s.pairs_consumed;
+        c->stats.depth_culled += s.pairs_culled;
         c->stats.batches_run += s.batches_run;
     }
     // adaptive policy for the next call (results are identical either way): batch when most list entries of a
@@ -403,6 +414,13 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
         for (size_t i = 0; i < nviews; ++i)
             for (int b = 0; b < MAX_BATCHES; ++b) any_large |= c->h_status[i].n_large[b] != 0;
         c->nobin_mode = !any_large;
+        {   // depth mode: next frame's front-to-back chunk thresholds span what this frame saw
+            const ViewStatus& z = c->h_status[nviews - 1];
+            if (z.zhi) {
+                const float lo = depth_unord_host(~z.zlo_inv), hi = depth_unord_host(z.zhi);
+                if (lo == lo && hi == hi && hi > lo) { c->z_lo = lo; c->z_hi = hi; }
+            }
+        }
         const ViewStatus& s = c->h_status[nviews - 1];
         if (c->force_batches >= 0) c->batched_mode = c->force_batches != 0;
         else if (!c->batched_mode) {
@@ -549,6 +567,7 @@ int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64
     c->batched_mode = c->force_batches > 0;      // the adaptive policy starts over with every mesh
     c->single_batch_pairs = 0;
     c->nobin_mode = false;
+    c->z_lo = 0.0f; c->z_hi = 1.0f;
     return rc;
 }
 

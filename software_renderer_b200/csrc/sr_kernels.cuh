@@ -46,6 +46,8 @@ struct ViewStatus {
     unsigned long long pairs_consumed;  // pairs the tile kernel actually processed (early-out feedback)
     unsigned seg_max;                   // slab lists: largest (tile, chunk) segment requested (> slab_cap -> frame is re-run)
     unsigned open_after_first;          // batched mode: tiles still open after the first batch
+    unsigned zlo_inv, zhi;              // depth mode: ~min / max of depth_ord(lower bound) over binned triangles
+    unsigned long long pairs_culled;    // depth mode: records rejected by their depth bound or never read
 };
 
 // Bin-list record of a large triangle (32 B = one sector): corners SORTED as R:271 leaves them and the sort
@@ -129,6 +131,8 @@ struct FrameParams {
     int batched;              // 1: several index-descending batches (depth off only)
     int slab_cap;             // > 0: tile lists are fixed-capacity slabs, slab_cap entries per (tile, chunk) segment,
                               //      filled directly by k_setup (no k_scan / k_bin_fill); 0: compact lists
+    float zthr[NCHUNK - 1];   // depth mode: ascending thresholds; tile-list chunk c holds triangles whose depth lower
+                              //   bound is >= zthr[c-1] (chunk 0: everything else), so lists run front to back
     int nobin;                // 1: speculative frame without binning kernels (the previous frame had no large
                               //    triangle); a large triangle is only counted and the host re-runs the frame
 };
@@ -329,8 +333,33 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, floa
             slot = __shfl_sync(0xffffffffu, base, 0) + __popc(m_large & ((1u << lane) - 1u));
             if (large) recs[slot] = TriRec{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, perm};
         }
-        // chunks are stored in DESCENDING index order inside each tile list
-        const int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
+        // depth off: chunks are stored in DESCENDING index order inside each tile list
+        // depth on : chunks run front to back by a rigorous lower bound of the triangle's depth over its clipped bbox
+        int cslot = NCHUNK - 1 - ((prim - bp.lo) >> bp.chunk_shift);
+        if (DEPTH && fp.slab_cap) {
+            cslot = 0;
+            float dlo = __int_as_float(0x7fc00000), zmin = 0.0f, zmax = 0.0f;
+            if (large) {
+                const BaryT bt = bary_setup(ax, ay, bx, by, cx, cy);
+                DepthSample m = depth_sample(bt, za, zb, zc, xmin, y0);
+#pragma unroll
+                for (int q = 1; q < 4; ++q) {
+                    const DepthSample t = depth_sample(bt, za, zb, zc, (q & 1) ? xmax : xmin, (q & 2) ? y1 : y0);
+                    m.d = fminf(m.d, t.d); m.a = fmaxf(m.a, t.a); m.b = fmaxf(m.b, t.b);
+                }
+                // the better of two rigorous bounds: over the clipped bbox rectangle, over the covered pixels
+                dlo = fmaxf(depth_lower_bound(m.d, m.a, m.b, za, zb, zc), depth_triangle_bound(bt, za, zb, zc, m.a, m.b));
+                if (!(fabsf(m.d) < __int_as_float(0x7f800000) && fabsf(m.a + m.b) < __int_as_float(0x7f800000))) dlo = __int_as_float(0x7fc00000);
+#pragma unroll
+                for (int q = 0; q < NCHUNK - 1; ++q) cslot += (dlo >= fp.zthr[q]) ? 1 : 0;    // NaN: chunk 0
+                zmin = fminf(za, fminf(zb, zc)); zmax = fmaxf(za, fmaxf(zb, zc));
+            }
+            // range of the binned triangles' corner depths: next frame's thresholds
+            const bool fin = large && fabsf(zmin) < __int_as_float(0x7f800000) && fabsf(zmax) < __int_as_float(0x7f800000);
+            const unsigned hi = __reduce_max_sync(0xffffffffu, fin ? depth_ord(zmax) : 0u);
+            const unsigned lo_inv = __reduce_max_sync(0xffffffffu, fin ? ~depth_ord(zmin) : 0u);
+            if (lane == 0 && hi) { atomicMax(&status->zhi, hi); atomicMax(&status->zlo_inv, lo_inv); }
+        }
         const int items = large ? (tx1 - tx0 + 1) * (ty1 - ty0 + 1) : 0;
         s_rect[threadIdx.x] = StagedRect{tx0, ty0, (tx1 - tx0 + 1) | (items > 2 ? 0x8000 : 0) | (cslot << 16), (int)slot};
         __syncwarp();
@@ -610,11 +639,17 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
     __shared__ unsigned s_off[NCHUNK + 1];                 // slab lists: prefix of the tile's 16 segment lengths
+    __shared__ __align__(16) unsigned s_wmax[8];           // depth mode: per-warp max of the pixels' depth_ord
+    __shared__ unsigned s_zord[NCHUNK];                    // depth mode: depth_ord of the chunk thresholds
 
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
     const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
     const bool late = fp.batched && bp.index > 0;                   // only later batches can meet retired tiles
+    if (DEPTH) {
+#pragma unroll
+        for (int q = 0; q < NCHUNK - 1; ++q) if (tid == q) s_zord[q] = depth_ord(fp.zthr[q]);
+    }
     if (late && status->tiles_done >= (unsigned)fp.ntiles) return;
 
     // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA launches
@@ -635,6 +670,15 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     }
     const unsigned v_in = v;
     const unsigned long long k_in = k;
+    // depth mode: farthest current depth over the tile's pixels (empty pixel = 0xffffffff = nothing can be rejected)
+    auto publish_zmax = [&]() {
+        const unsigned wm = __reduce_max_sync(0xffffffffu, inside ? (unsigned)(k >> 32) : 0u);
+        if ((tid & 31) == 0) s_wmax[tid >> 5] = wm;
+    };
+    auto read_zmax = [&]() -> unsigned {
+        const uint4 a = *reinterpret_cast<const uint4*>(&s_wmax[0]), b = *reinterpret_cast<const uint4*>(&s_wmax[4]);
+        return max(max(max(a.x, a.y), max(a.z, a.w)), max(max(b.x, b.y), max(b.z, b.w)));
+    };
 
     const size_t seg = (size_t)tile * NCHUNK;
     const bool slab = fp.slab_cap > 0 && !fp.nobin;
@@ -647,6 +691,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     const int yy = ty * TILE + row;
 
     __syncthreads();                                       // previous tile of this CTA is done with shared memory
+    if (DEPTH) publish_zmax();
     if (slab) {
         // the tile's list = its 16 segments, highest index chunk first; lengths are read and re-armed here
         if (tid < 32) {
@@ -667,6 +712,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         if (tid == 0 && end) atomicAdd(&status->total_pairs[bp.index], end);
     }
     unsigned p = begin;
+    unsigned n_culled = 0;
 
     // software pipeline run by warp 0: lanes 0..15 bring the records of the NEXT round global -> shared with cp.async
     // (no registers held) while the current round is processed; the block barrier that ends the round publishes them.
@@ -698,15 +744,53 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             if (tid < TILE_BATCH && p + TILE_BATCH + tid < end) fetch(cur ^ 1, p + TILE_BATCH + tid);
             __pipeline_commit();
         }
+        unsigned zmax_u = 0xffffffffu;
+        if (DEPTH) {
+            zmax_u = read_zmax();
+            // front-to-back lists: every record from position p on sits in chunk >= c, whose triangles cannot go
+            // below zthr[c-1]; once that is beyond the farthest pixel of the tile, nothing left can pass R:258
+            if (slab) {
+                int c = 0;
+#pragma unroll
+                for (int step = NCHUNK / 2; step > 0; step >>= 1) if (s_off[c + step] <= p) c += step;
+                if (c > 0 && s_zord[c - 1] > zmax_u) break;
+            }
+        }
         // per-edge reciprocals of this round's triangles: rows 0..2 of a triangle's 16 lanes compute one each
         if (j < n && row < 3) {
             const TriRec& t = s_rec[cur][j];
             s_rcp[j][row] = edge_rcp(row == 0 ? t.y1 - t.y0 : (row == 1 ? t.y2 - t.y1 : t.y2 - t.y0));
         }
+        if (DEPTH && j < n && row == 0) {
+            const TriRec& t = s_rec[cur][j];
+            int oc[6];
+            unsort_corners(t, oc);
+            s_bt[j] = bary_setup(oc[0], oc[1], oc[2], oc[3], oc[4], oc[5]);
+            const float4 z = in.ztri[t.prim];
+            s_z[j][0] = z.x; s_z[j][1] = z.y; s_z[j][2] = z.z;
+        }
         __syncwarp();
+        bool culled = false;
+        if (DEPTH) {
+            // reject the whole (triangle, tile) record when a rigorous lower bound of its depth over the tile's pixels
+            // is beyond the farthest pixel: each lane samples one corner pixel of the tile, xor-shuffles reduce
+            const int jq = j < n ? j : 0;
+            DepthSample m = depth_sample(s_bt[jq], s_z[jq][0], s_z[jq][1], s_z[jq][2],
+                                         (row & 1) ? x_hi : x_lo, (row & 2) ? min(ty * TILE + TILE - 1, fp.height - 1) : ty * TILE);
+#pragma unroll
+            for (int d = 1; d <= 2; d <<= 1) {
+                m.d = fminf(m.d, __shfl_xor_sync(0xffffffffu, m.d, d));
+                m.a = fmaxf(m.a, __shfl_xor_sync(0xffffffffu, m.a, d));
+                m.b = fmaxf(m.b, __shfl_xor_sync(0xffffffffu, m.b, d));
+            }
+            // a NaN sample needs an inf/NaN constant of the triangle, which makes the margin non-finite at some corner:
+            // then dlo is not finite and nothing is rejected
+            const float dlo = depth_lower_bound(m.d, m.a, m.b, s_z[jq][0], s_z[jq][1], s_z[jq][2]);
+            culled = fabsf(dlo) < __int_as_float(0x7f800000) && depth_ord(dlo) > zmax_u;
+        }
         {   // phase A: (triangle j, row) -> column mask
             unsigned mask = 0;
-            if (j < n) {
+            if (j < n && !culled) {
                 const TriRec& t = s_rec[cur][j];
                 const SortedTri s = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                 if (yy >= s.y0 && yy <= s.y2 && yy < fp.height) {
@@ -716,16 +800,10 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                     r = min(r, x_hi);
                     if (l <= r) mask = ((2u << (r - l)) - 1u) << (l - x_lo);
                 }
-                if (row == 0) {
-                    s_prim[j] = t.prim;
-                    if (DEPTH) {
-                        int oc[6];
-                        unsort_corners(t, oc);
-                        s_bt[j] = bary_setup(oc[0], oc[1], oc[2], oc[3], oc[4], oc[5]);
-                        const float4 z = in.ztri[t.prim];
-                        s_z[j][0] = z.x; s_z[j][1] = z.y; s_z[j][2] = z.z;
-                    }
-                }
+            }
+            if (j < n && row == 0) {
+                s_prim[j] = s_rec[cur][j].prim;
+                if (DEPTH && culled) ++n_culled;
             }
             s_mask[row][j] = (unsigned short)mask;         // zero for j >= n
         }
@@ -755,6 +833,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         cur ^= 1;
         if (producer) __pipeline_wait_prior(0);            // next records landed (made visible by the barrier below)
         if (DEPTH) {
+            publish_zmax();
             __syncthreads();
         } else {
             // every remaining pair of this batch has prim < thr (chunks are stored in descending order)
@@ -765,6 +844,14 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     }
     __pipeline_wait_prior(0);
     if (tid == 0 && p > begin) atomicAdd(&status->pairs_consumed, (unsigned long long)(p - begin));
+    if (DEPTH) {
+        // records rejected by their bound (counted by the row-0 lanes) + records never read
+        unsigned tot = n_culled;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
+        if ((tid & 31) == 0 && tot) atomicAdd(&status->pairs_culled, (unsigned long long)tot);
+        if (tid == 0 && end > p) atomicAdd(&status->pairs_culled, (unsigned long long)(end - p));
+    }
 
     bool shade_now = true;
     if (fp.batched && !bp.final_batch) {

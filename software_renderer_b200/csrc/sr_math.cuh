@@ -190,4 +190,50 @@ __device__ __forceinline__ unsigned long long depth_key(float d, unsigned prim) 
     return ((unsigned long long)u << 32) | prim;
 }
 
+// ---- conservative depth bounds (depth mode: hierarchical rejection) ----------------------------------------------
+// ordered-uint image of a float (monotone: a < b  =>  ord(a) < ord(b); -0 sorts just below +0)
+__device__ __forceinline__ unsigned depth_ord(float d) {
+    const unsigned u = __float_as_uint(d);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float depth_unord(unsigned o) {
+    return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
+// One corner sample for depth_lower_bound: the depth R:257 computes at pixel (x, y), and the magnitudes that scale
+// its rounding error.
+struct DepthSample { float d, a, b; };
+__device__ __forceinline__ DepthSample depth_sample(const BaryT& t, float za, float zb, float zc, int x, int y) {
+    const float px = __fadd_rn(__int2float_rn(x), 0.5f), py = __fadd_rn(__int2float_rn(y), 0.5f);
+    const float dx = __fsub_rn(px, t.cfx), dy = __fsub_rn(py, t.cfy);
+    DepthSample s;
+    s.d = blend3(za, zb, zc, bary_weights(t, x, y));
+    s.a = fabsf(t.c0x * dx) + fabsf(t.c1x * dy);
+    s.b = fabsf(t.c0y * dx) + fabsf(t.c1y * dy);
+    return s;
+}
+// Lower bound of every depth value R:257 can produce for this triangle at the pixels of a rectangle, given the
+// samples at the rectangle's four corner pixels (dmin = smallest sample, amax / bmax = largest magnitudes).
+// In real arithmetic the depth is affine in (x, y) (the per-triangle constants are fixed floats), so its minimum
+// over the rectangle sits at a corner; the float evaluation differs from the real one by at most
+// ~8u (|za| A + |zb| B + |zc| (1 + A + B)), u = 2^-24, A = |c0x dx| + |c1x dy|, B likewise (each product, sum and
+// the two subtractions of wc round once; A and B are convex, so their maxima are at corners too).  The margin below
+// uses 2^-17 (16x that) twice: once for the interior pixel, once for the corner sample.  A non-finite result means
+// "no bound" and callers must not reject on it.
+__device__ __forceinline__ float depth_lower_bound(float dmin, float amax, float bmax, float za, float zb, float zc) {
+    const float e = (fabsf(za) * amax + fabsf(zb) * bmax + fabsf(zc) * (1.0f + amax + bmax)) * 0x1p-16f;
+    return dmin - e - 1e-37f;
+}
+
+// Lower bound of the depth at EVERY pixel the span rule can cover for this triangle.  Each covered pixel centre lies
+// on a row that crosses the real triangle (af, bf, cf) and within one pixel, horizontally, of that crossing (both
+// span ends are truncations of the exact edge positions, or a vertex on the collapsed last row), so the depth there
+// is at least min(za, zb, zc) - |dD/dx| - rounding, with dD/dx = za c0x + zb c0y - zc (c0x + c0y).
+// amax / bmax: the DepthSample magnitudes maximised over a rectangle that holds all covered pixels (clipped bbox).
+__device__ __forceinline__ float depth_triangle_bound(const BaryT& t, float za, float zb, float zc, float amax, float bmax) {
+    const float gx = (za * t.c0x + zb * t.c0y) - zc * (t.c0x + t.c0y);
+    const float slack = (fabsf(za * t.c0x) + fabsf(zb * t.c0y) + fabsf(zc * t.c0x) + fabsf(zc * t.c0y)) * 0x1p-16f;
+    const float e = (fabsf(za) * amax + fabsf(zb) * bmax + fabsf(zc) * (1.0f + amax + bmax)) * 0x1p-16f;
+    return fminf(za, fminf(zb, zc)) - fabsf(gx) - slack - e - 1e-37f;
+}
+
 }  // namespace sr

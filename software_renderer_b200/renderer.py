@@ -46,7 +46,7 @@ class SrStats(ctypes.Structure):
     _fields_ = [
         ("primitives", ctypes.c_uint64), ("domain_skipped", ctypes.c_uint64), ("small_tris", ctypes.c_uint64),
         ("binned_tris", ctypes.c_uint64), ("tile_pairs", ctypes.c_uint64), ("bin_regrows", ctypes.c_uint64),
-        ("pairs_consumed", ctypes.c_uint64), ("batches_run", ctypes.c_uint64), ("nobin_reruns", ctypes.c_uint64),
+        ("pairs_consumed", ctypes.c_uint64), ("batches_run", ctypes.c_uint64), ("depth_culled", ctypes.c_uint64), ("nobin_reruns", ctypes.c_uint64),
         ("gpu_launches", ctypes.c_uint64), ("gpu_ms", ctypes.c_float),
     ]
 

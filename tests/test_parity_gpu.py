@@ -374,3 +374,57 @@ def test_resolve_kernel_odd_sizes(size, depth_test):
             assert r.stats()["nobin_reruns"] == 0 and r.stats()["binned_tris"] == 0
     finally:
         r.close()
+
+
+def _layered(n, seed, zfun, spread=1.2, size=0.9):
+    rng = np.random.default_rng(seed)
+    c = rng.uniform(-spread, spread, size=(n, 1, 2))
+    xy = (c + rng.uniform(-size, size, size=(n, 3, 2))).reshape(-1, 2)
+    z = zfun(rng, n).astype(np.float64).reshape(-1)
+    xyz = np.concatenate([xy, z[:, None]], 1).astype(np.float32)
+    rgb = rng.uniform(0, 1, size=(3 * n, 3)).astype(np.float32)
+    return S.pack_vertices(xyz, rgb), np.arange(3 * n, dtype=np.int64)
+
+
+@pytest.mark.parametrize("case", ["front_last", "front_first", "ties", "tilted", "slivers", "huge_z", "negative_w"])
+def test_depth_bounds_never_change_the_image(case):
+    """Depth mode rejects (triangle, tile) records by a conservative depth bound and stops a tile's front-to-back
+    list early; the image must stay bit-exact whatever the layering, including exact ties, slivers with huge
+    barycentric weights and non-finite depths."""
+    n = 3000
+    W, H = 640, 480
+    m = I4
+    if case == "front_last":            # nearest triangles have the highest indices
+        v, i = _layered(n, 1, lambda r, k: np.repeat(np.linspace(0.9, 0.1, k), 3))
+    elif case == "front_first":
+        v, i = _layered(n, 2, lambda r, k: np.repeat(np.linspace(0.1, 0.9, k), 3))
+    elif case == "ties":                # a few exact depth levels: the earliest index must win every tie
+        v, i = _layered(n, 3, lambda r, k: np.repeat(r.integers(0, 4, size=k) * 0.25, 3))
+    elif case == "tilted":              # per-corner depths: planes intersect inside tiles
+        v, i = _layered(n, 4, lambda r, k: r.uniform(0.0, 1.0, size=3 * k))
+    elif case == "slivers":
+        v, i = _layered(n, 5, lambda r, k: r.uniform(-1.0, 1.0, size=3 * k))
+        xyz = v[:, :3].copy().reshape(-1, 3, 3)
+        xyz[:, 2, :2] = xyz[:, 1, :2] + (xyz[:, 1, :2] - xyz[:, 0, :2]) * 1e-3      # nearly collinear corners
+        v = S.pack_vertices(xyz.reshape(-1, 3), v[:, 4:7])
+    elif case == "huge_z":              # products overflow to inf, inf - inf gives NaN depths: neither ever passes R:258
+        def z(r, k):
+            out = r.uniform(0.0, 1.0, size=3 * k)
+            out[r.integers(0, 3 * k, size=k // 8)] = 3.0e38
+            out[r.integers(0, 3 * k, size=k // 8)] = -3.0e38
+            out[r.integers(0, 3 * k, size=k // 8)] = 1.0e-42
+            return out
+        v, i = _layered(n, 6, z)
+    else:                               # perspective with w = z + 1 crossing zero
+        v, i = _layered(n, 7, lambda r, k: r.uniform(-1.6, 1.0, size=3 * k), spread=0.8, size=0.5)
+        m = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0], [0, 0, 1, 1]], np.float32)
+    r = srb.CudaRenderer(0)
+    try:
+        for k in range(2):              # second frame uses thresholds learned from the first
+            with np.errstate(all="ignore"):
+                assert_same(r, v, i, m, W, H, depth_test=True)
+        if case == "front_first":
+            s = r.stats()
+            assert s["depth_culled"] > 0.5 * s["tile_pairs"]
+    finally:
+        r.close()
