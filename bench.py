@@ -289,7 +289,8 @@ def run_cuda(args):
         hbm, peak_kind = peaks()
         # algorithmic bytes: indices 12 B/tri, vertex xyz+rgb 24 B, colour+depth 8 B/pixel, split over
         # the kernels that touch them
-        alg = {"k_transform": 12 * nverts, "k_setup": 12 * ntris, "k_tile": 12 * nverts + 8 * W * H}
+        alg = {"k_transform": 12 * nverts, "k_setup": 12 * ntris, "k_tile": 12 * nverts + 8 * W * H,
+               "k_resolve": 12 * nverts + 8 * W * H}
         top = max(acc, key=acc.get) if acc else "k_tile"
         top_ms = acc.get(top, float("nan"))
         top_bytes = alg.get(top, 0)

@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, floa
             };
             a = corner(i0); b = corner(i1); c = corner(i2);
         } else {
-            a = sv[i0]; b = sv[i1]; c = sv[i2];
+            a = __ldg(&sv[i0]); b = __ldg(&sv[i1]); c = __ldg(&sv[i2]);     // read-only path (sv is written only under XFORM)
         }
         if (!(in_domain(a.x) && in_domain(a.y) && in_domain(b.x) && in_domain(b.y) && in_domain(c.x) && in_domain(c.y))) {
             skipped = true;                                         // the reference traps here (R:251, R:271)
