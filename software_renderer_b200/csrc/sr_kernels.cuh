@@ -191,7 +191,7 @@ struct XformIn {
     float fw, fh;
 };
 template <bool DEPTH, bool BIN, bool XFORM>
-__global__ void __launch_bounds__(256) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
+__global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
