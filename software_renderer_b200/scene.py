@@ -232,3 +232,32 @@ def triangle_soup(count: int, width: int, height: int, seed: int = 0x5EED0003,
 def algorithmic_bytes(ntris: int, nverts: int, width: int, height: int) -> int:
     """each index once as int32, each vertex once as xyz+rgb, each pixel's colour and depth once."""
     return 12 * ntris + 24 * nverts + 8 * width * height
+
+
+# ---------------------------------------------------------------------------------------------
+# headless image output (replaces the MTKView blit + present of App.swift:103-105)
+# ---------------------------------------------------------------------------------------------
+def write_ppm(path: str, bgra: np.ndarray) -> None:
+    """Binary PPM (P6) of a (H, W, 4) BGRA8 image as the renderer writes it (Pixel = b,g,r,a, Renderer.swift:44-49)."""
+    img = np.asarray(bgra, dtype=np.uint8)
+    h, w = img.shape[:2]
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (w, h))
+        f.write(np.ascontiguousarray(img[..., 2::-1]).tobytes())
+
+
+def write_png(path: str, bgra: np.ndarray) -> None:
+    """RGBA PNG (zlib only, no imaging dependency) of a (H, W, 4) BGRA8 image."""
+    import struct
+    import zlib
+    img = np.asarray(bgra, dtype=np.uint8)
+    h, w = img.shape[:2]
+    rgba = np.ascontiguousarray(img[..., [2, 1, 0, 3]])
+    raw = np.concatenate([np.zeros((h, 1), np.uint8), rgba.reshape(h, w * 4)], axis=1).tobytes()   # filter 0 per row
+
+    def chunk(tag: bytes, data: bytes) -> bytes:
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 6, 0, 0, 0))
+                + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))

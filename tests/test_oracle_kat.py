@@ -152,3 +152,25 @@ def test_cube_scene_config1():
         assert rc == 0 and st["primitives"] == 12 and (c[..., 3] > 0).sum() > 20000
         assert prev is None or not np.array_equal(prev, c)
         prev = c
+
+
+def test_image_writers_roundtrip(tmp_path):
+    import struct
+    import zlib
+    rng = np.random.default_rng(1)
+    img = rng.integers(0, 256, size=(7, 5, 4), dtype=np.uint8)
+    S.write_ppm(str(tmp_path / "a.ppm"), img)
+    raw = (tmp_path / "a.ppm").read_bytes()
+    assert raw.startswith(b"P6\n5 7\n255\n") and raw[11:] == img[..., 2::-1].tobytes()
+    S.write_png(str(tmp_path / "a.png"), img)
+    png = (tmp_path / "a.png").read_bytes()
+    assert png[:8] == b"\x89PNG\r\n\x1a\n" and struct.unpack(">II", png[16:24]) == (5, 7)
+    pos, idat = 8, b""
+    while pos < len(png):
+        n, tag = struct.unpack(">I", png[pos:pos + 4])[0], png[pos + 4:pos + 8]
+        assert zlib.crc32(png[pos + 4:pos + 8 + n]) & 0xFFFFFFFF == struct.unpack(">I", png[pos + 8 + n:pos + 12 + n])[0]
+        if tag == b"IDAT":
+            idat += png[pos + 8:pos + 8 + n]
+        pos += 12 + n
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(7, 1 + 5 * 4)
+    assert (rows[:, 0] == 0).all() and np.array_equal(rows[:, 1:].reshape(7, 5, 4), img[..., [2, 1, 0, 3]])
