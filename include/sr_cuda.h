@@ -130,6 +130,25 @@ int sr_get_kernel_times(sr_ctx* ctx, const char** names, float* ms, int cap);
 /* Enables per-kernel CUDA-event timing (adds events between kernels; off by default). */
 int sr_set_profiling(sr_ctx* ctx, int enabled);
 
+/* -- legacy 2-D immediate-mode API of Renderer.swift ------------------------------------ */
+/* Replaces draw(rect:with:in:) R:376-383, draw(circle:with:in:) R:385-403, draw(line:with:in:) R:405-419 and
+ * draw(triangle:with:in:) R:421-465.  The commands run in order on one caller-owned host BGRA image (in-out:
+ * pixels no command touches keep their contents), each as a CUDA kernel on a device copy of the image.
+ *   SR_2D_RECT     p = {x, y, w, h}: rows y ..< y+w step sign(w), columns x ..< x+h step sign(h) — the reference
+ *                  swaps w and h (R:378-379) and so does this; unchecked stores of `color`.
+ *   SR_2D_CIRCLE   p = {x, y, r}: dy, dx in -r ..< r, smooth-step edge, writes only the blue channel (R:401).
+ *   SR_2D_LINE     p = {x0, y0, x1, y1}: float DDA with `.rounded()`, bounds-checked stores of `color`.
+ *   SR_2D_TRIANGLE p = {ax, ay, bx, by, cx, cy}: integer corners, the span rule of R:467-494, colour = weights.
+ * Error behaviour: the reference writes through a raw pointer for RECT and CIRCLE (out-of-image footprints corrupt
+ * memory) and a zero w, h or r traps in stride(by: 0); such a command returns SR_ERR_DOMAIN and nothing is drawn. */
+enum { SR_2D_RECT = 0, SR_2D_CIRCLE = 1, SR_2D_LINE = 2, SR_2D_TRIANGLE = 3 };
+typedef struct sr_cmd2d {
+    int32_t kind;
+    int32_t p[6];
+    uint8_t color[4]; /* b, g, r, a (Pixel, R:44-49) */
+} sr_cmd2d;
+int sr_draw2d(sr_ctx* ctx, const sr_cmd2d* cmds, size_t ncmds, int width, int height, uint8_t* color_bgra);
+
 #ifdef __cplusplus
 }
 #endif

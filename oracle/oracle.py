@@ -64,6 +64,8 @@ def lib():
         L.sr_oracle_weights.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]
         L.sr_oracle_pack_pixel.restype = None
         L.sr_oracle_pack_pixel.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.sr_oracle_draw2d.restype = ctypes.c_int
+        L.sr_oracle_draw2d.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -119,3 +121,10 @@ def pack_pixel(rgb):
     out = np.empty(4, dtype=np.uint8)
     lib().sr_oracle_pack_pixel(c.ctypes.data, out.ctypes.data)
     return out
+
+
+def draw2d(cmd_array, ncmds, image):
+    """Legacy 2-D API (Renderer.swift:376-465) on a (H, W, 4) BGRA8 image, in place.  `cmd_array` is a ctypes array
+    with the sr_oracle_cmd2d layout (software_renderer_b200.renderer.pack_cmds builds one)."""
+    assert image.dtype == np.uint8 and image.flags.c_contiguous
+    return lib().sr_oracle_draw2d(cmd_array, ncmds, image.shape[1], image.shape[0], image.ctypes.data)

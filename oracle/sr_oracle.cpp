@@ -4,7 +4,9 @@
 // as Swift compiles them.
 #include "sr_oracle.h"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -261,5 +263,93 @@ void sr_oracle_weights(const int64_t* abc, int64_t x, int64_t y, float* out3) {
 }
 
 void sr_oracle_pack_pixel(const float* rgb, uint8_t* out) { pack_pixel(F3{rgb[0], rgb[1], rgb[2]}, out); }
+
+// ---- legacy 2-D immediate-mode API (R:376-465) -------------------------------------------------------------------
+namespace {
+inline int sgn(int v) { return (v > 0) - (v < 0); }
+inline bool cmd2d_in_domain(const sr_oracle_cmd2d& c, int W, int H) {
+    if (c.kind == SR_ORACLE_2D_RECT) {
+        const int x = c.p[0], y = c.p[1], w = c.p[2], h = c.p[3];
+        if (w == 0 || h == 0) return false;                               // stride(by: 0) traps
+        const int ya = y, yb = y + w - sgn(w), xa = x, xb = x + h - sgn(h);   // first / last row and column touched
+        return std::min(ya, yb) >= 0 && std::max(ya, yb) < H && std::min(xa, xb) >= 0 && std::max(xa, xb) < W;
+    }
+    if (c.kind == SR_ORACLE_2D_CIRCLE) {
+        const int x = c.p[0], y = c.p[1], r = c.p[2];
+        if (r == 0) return false;
+        const int a = -r, b = r - sgn(r);
+        return y + std::min(a, b) >= 0 && y + std::max(a, b) < H && x + std::min(a, b) >= 0 && x + std::max(a, b) < W;
+    }
+    return c.kind == SR_ORACLE_2D_LINE || c.kind == SR_ORACLE_2D_TRIANGLE;
+}
+inline void store_checked(uint8_t* img, int W, int H, int64_t x, int64_t y, const uint8_t* px) {   // Image subscript set, R:30-36
+    if (x >= 0 && x < W && y >= 0 && y < H) std::memcpy(img + 4 * ((size_t)y * W + (size_t)x), px, 4);
+}
+}  // namespace
+
+int sr_oracle_draw2d(const sr_oracle_cmd2d* cmds, size_t n, int W, int H, uint8_t* img) {
+    if (!img || W <= 0 || H <= 0 || (n && !cmds)) return SR_ORACLE_ERR_ARG;
+    for (size_t k = 0; k < n; ++k) {
+        if (cmds[k].kind < SR_ORACLE_2D_RECT || cmds[k].kind > SR_ORACLE_2D_TRIANGLE) return SR_ORACLE_ERR_ARG;
+        if (!cmd2d_in_domain(cmds[k], W, H)) return SR_ORACLE_ERR_DOMAIN;
+    }
+    for (size_t k = 0; k < n; ++k) {
+        const sr_oracle_cmd2d& c = cmds[k];
+        if (c.kind == SR_ORACLE_2D_RECT) {                                  // R:376-383 (w drives y, h drives x)
+            const int x0 = c.p[0], y0 = c.p[1], w = c.p[2], h = c.p[3];
+            for (int y = y0; y != y0 + w; y += sgn(w))
+                for (int x = x0; x != x0 + h; x += sgn(h)) std::memcpy(img + 4 * ((size_t)y * W + x), c.color, 4);
+        } else if (c.kind == SR_ORACLE_2D_CIRCLE) {                         // R:385-403
+            const int cx = c.p[0], cy = c.p[1], ri = c.p[2];
+            const float r = (float)ri;
+            for (int dy = -ri; dy != ri; dy += sgn(ri))
+                for (int dx = -ri; dx != ri; dx += sgn(ri)) {
+                    const float px = (float)dx + 0.5f, py = (float)dy + 0.5f;
+                    const float l = sqrtf(px * px + py * py);
+                    float d;
+                    if (l < r - 2.0f) {
+                        d = 1.0f;
+                    } else {
+                        const float e0 = r + 2.0f, e1 = r - 2.0f;
+                        const float t = clamp01((l - e0) / (e1 - e0));
+                        d = clamp01(t * t * (3.0f - 2.0f * t));
+                    }
+                    uint8_t px4[4] = {(uint8_t)(clamp01(d) * 255.0f), 0, 0, 255};   // .floats(b: d, g: 0, r: 0, a: 1)
+                    std::memcpy(img + 4 * ((size_t)(cy + dy) * W + (cx + dx)), px4, 4);
+                }
+        } else if (c.kind == SR_ORACLE_2D_LINE) {                           // R:405-419
+            const int dx = c.p[2] - c.p[0], dy = c.p[3] - c.p[1];
+            const int steps = std::max(std::abs(dx), std::abs(dy));
+            const float xs = (float)dx / (float)steps, ys = (float)dy / (float)steps;
+            float x = (float)c.p[0], y = (float)c.p[1];
+            for (int s = 0; s < steps; ++s) {
+                store_checked(img, W, H, (int64_t)roundf(x), (int64_t)roundf(y), c.color);
+                x += xs;
+                y += ys;
+            }
+        } else {                                                            // R:421-465
+            L2 v[3] = {{c.p[0], c.p[1]}, {c.p[2], c.p[3]}, {c.p[4], c.p[5]}};
+            L2 s[3] = {v[0], v[1], v[2]};
+            for (int i = 1; i < 3; ++i)                                     // stable insertion sort, strict < on int y
+                for (int j = i; j > 0 && s[j].y < s[j - 1].y; --j) std::swap(s[j], s[j - 1]);
+            const L2 right[2] = {s[0], s[2]};
+            for (int64_t y = s[0].y; y <= s[2].y; ++y) {
+                int64_t l = interpolate(s, 3, y), r = interpolate(right, 2, y);
+                if (l > r) std::swap(l, r);
+                if (y < 0 || y >= H) continue;                              // every store of the row fails the bounds check
+                for (int64_t x = std::max<int64_t>(l, 0); x <= std::min<int64_t>(r, W - 1); ++x) {
+                    const F3 ws = triangle_ws(v[0], v[1], v[2], (float)x + 0.5f, (float)y + 0.5f);
+                    // (ac*ws.x + bc*ws.y + cc*ws.z) * a with unit colours and a = 1: each channel is its weight plus zeros
+                    const F3 col = {((ws.x * 1.0f + ws.y * 0.0f) + ws.z * 0.0f) * 1.0f, ((ws.x * 0.0f + ws.y * 1.0f) + ws.z * 0.0f) * 1.0f,
+                                    ((ws.x * 0.0f + ws.y * 0.0f) + ws.z * 1.0f) * 1.0f};
+                    uint8_t px4[4];
+                    pack_pixel(col, px4);
+                    store_checked(img, W, H, x, y, px4);
+                }
+            }
+        }
+    }
+    return SR_ORACLE_OK;
+}
 
 }  // extern "C"

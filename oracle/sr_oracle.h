@@ -81,6 +81,30 @@ void sr_oracle_weights(const int64_t* abc_xy, int64_t x, int64_t y, float* out3)
 /* Pixel(float3:) (R:117-128): rgb floats -> 4 bytes b,g,r,a */
 void sr_oracle_pack_pixel(const float* rgb, uint8_t* out_bgra);
 
+/*
+ * Legacy 2-D immediate-mode API of the same file: draw(rect:) R:376-383, draw(circle:)
+ * R:385-403, draw(line:) R:405-419, draw(triangle:with:in:) R:421-465.  Commands run in order on one BGRA image.
+ *   RECT     p = {x, y, w, h}: rows y ..< y+w step sign(w), columns x ..< x+h step sign(h) (w and h are swapped in
+ *            the reference, R:378-379), raw pointer stores of `color` (no bounds check).
+ *   CIRCLE   p = {x, y, r}: dy, dx in -r ..< r; d = 1 if |p| < r-2 else clamp(smoothstep(r+2, r-2, |p|), 0, 1) with
+ *            p = (dx, dy) + 0.5; stores Pixel.floats(b: d, g: 0, r: 0, a: 1) through the raw pointer; `color` unused.
+ *   LINE     p = {x0, y0, x1, y1}: float DDA, max(|dx|,|dy|) steps, x and y accumulated in float, `.rounded()`
+ *            (to nearest, ties away from zero), bounds-checked store of `color`.
+ *   TRIANGLE p = {ax, ay, bx, by, cx, cy}: integer corners, stable sort on int y, the span rule of R:467-494,
+ *            colour = the barycentric weights (r = ws.x, g = ws.y, b = ws.z), bounds-checked stores.
+ * Apple `simd` pieces defined here (not in the reference tree): length(p) = sqrtf(x*x + y*y) with separately rounded
+ * products and sum; smoothstep(e0, e1, x) = t*t*(3 - 2*t), t = clamp((x - e0) / (e1 - e0), 0, 1).
+ * Valid domain (the reference corrupts memory or traps outside it): RECT and CIRCLE footprints inside the image,
+ * w, h, r != 0 (a zero stride traps); otherwise SR_ORACLE_ERR_DOMAIN and NOTHING is drawn.
+ */
+enum { SR_ORACLE_2D_RECT = 0, SR_ORACLE_2D_CIRCLE = 1, SR_ORACLE_2D_LINE = 2, SR_ORACLE_2D_TRIANGLE = 3 };
+typedef struct sr_oracle_cmd2d {
+    int32_t kind;
+    int32_t p[6];
+    uint8_t color[4]; /* b, g, r, a */
+} sr_oracle_cmd2d;
+int sr_oracle_draw2d(const sr_oracle_cmd2d* cmds, size_t n, int width, int height, uint8_t* color_bgra);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,6 +5,6 @@ zhvrnkov/software-renderer (Renderer.render(renderPass:), Renderer.swift:204-230
   renderer.py     host-side mirror of the reference interface (RenderPass, PrimitiveType, CudaRenderer)
   scene.py        caller-side scene code: procedural meshes, baked colours, transform composition
 """
-from .renderer import (CudaRenderer, DomainError, Image, PrimitiveType, RenderPass, SrError, load_library,  # noqa: F401
+from .renderer import (Cmd2D, CudaRenderer, DomainError, Image, PrimitiveType, RenderPass, SrError, load_library,  # noqa: F401
                        ABI_SYMBOLS, LIB_PATH)
 from . import scene  # noqa: F401

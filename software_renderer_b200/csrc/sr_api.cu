@@ -688,6 +688,68 @@ int sr_render_pass(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const in
     return sr_render(c, transform, prim, W, H, color, depth, flags);
 }
 
+int sr_draw2d(sr_ctx* c, const sr_cmd2d* cmds, size_t n, int W, int H, uint8_t* color) {
+    if (!c) return SR_ERR_ARG;
+    if (!color || (n && !cmds) || W <= 0 || H <= 0 || (size_t)W * H > (1u << 30)) return fail(c, SR_ERR_ARG, "sr_draw2d: bad argument");
+    auto sgn = [](int v) { return (v > 0) - (v < 0); };
+    for (size_t k = 0; k < n; ++k) {                       // valid domain first: nothing is drawn if any command is outside it
+        const sr_cmd2d& q = cmds[k];
+        bool ok = q.kind >= SR_2D_RECT && q.kind <= SR_2D_TRIANGLE;
+        if (!ok) return fail(c, SR_ERR_ARG, "sr_draw2d: unknown command");
+        if (q.kind == SR_2D_RECT) {
+            const long long x = q.p[0], y = q.p[1], w = q.p[2], h = q.p[3];
+            ok = w != 0 && h != 0;
+            if (ok) {
+                const long long yb = y + w - sgn((int)w), xb = x + h - sgn((int)h);
+                ok = std::min(y, yb) >= 0 && std::max(y, yb) < H && std::min(x, xb) >= 0 && std::max(x, xb) < W;
+            }
+        } else if (q.kind == SR_2D_CIRCLE) {
+            const long long x = q.p[0], y = q.p[1], r = q.p[2];
+            ok = r != 0;
+            if (ok) {
+                const long long a = -r, b = r - sgn((int)r);
+                ok = y + std::min(a, b) >= 0 && y + std::max(a, b) < H && x + std::min(a, b) >= 0 && x + std::max(a, b) < W;
+            }
+        }
+        if (!ok) return fail(c, SR_ERR_DOMAIN, "sr_draw2d: rect/circle footprint outside the image or zero extent "
+                                               "(the reference writes through a raw pointer / traps, Renderer.swift:376-403)");
+    }
+    SR_CUDA(c, cudaSetDevice(c->device));
+    if (c->pending.active) { int rc = sr_sync(c); if (rc == SR_ERR_CUDA) return rc; }
+    cudaStream_t st = c->stream;
+    const size_t npx = (size_t)W * H;
+    SR_CUDA(c, c->out_color[0].reserve(4 * npx));
+    unsigned* img = reinterpret_cast<unsigned*>(c->out_color[0].p);
+    SR_CUDA(c, cudaMemcpyAsync(img, color, 4 * npx, cudaMemcpyHostToDevice, st));
+    c->launches = 0;
+    for (size_t k = 0; k < n; ++k) {
+        const sr_cmd2d& q = cmds[k];
+        unsigned col;
+        std::memcpy(&col, q.color, 4);
+        if (q.kind == SR_2D_RECT) {
+            const size_t cnt = (size_t)std::abs((long long)q.p[2]) * (size_t)std::abs((long long)q.p[3]);
+            k2d_rect<<<div_up(cnt, 256), 256, 0, st>>>(img, W, q.p[0], q.p[1], q.p[2], q.p[3], col);
+        } else if (q.kind == SR_2D_CIRCLE) {
+            const size_t side = 2 * (size_t)std::abs((long long)q.p[2]);
+            k2d_circle<<<div_up(side * side, 256), 256, 0, st>>>(img, W, q.p[0], q.p[1], q.p[2]);
+        } else if (q.kind == SR_2D_LINE) {
+            k2d_line<<<1, 32, 0, st>>>(img, W, H, q.p[0], q.p[1], q.p[2], q.p[3], col);
+        } else {
+            const long long ylo = std::max<long long>(std::min({q.p[1], q.p[3], q.p[5]}), 0);
+            const long long yhi = std::min<long long>(std::max({q.p[1], q.p[3], q.p[5]}), H - 1);
+            if (yhi >= ylo) k2d_triangle<<<div_up((size_t)(yhi - ylo + 1), 128), 128, 0, st>>>(img, W, H, q.p[0], q.p[1], q.p[2], q.p[3], q.p[4], q.p[5]);
+        }
+        c->launches++;
+    }
+    SR_CUDA(c, cudaGetLastError());
+    SR_CUDA(c, cudaMemcpyAsync(color, img, 4 * npx, cudaMemcpyDeviceToHost, st));
+    SR_CUDA(c, cudaStreamSynchronize(st));
+    c->stats = sr_stats{};
+    c->stats.primitives = n;
+    c->stats.gpu_launches = c->launches;
+    return SR_OK;
+}
+
 int sr_get_stats(sr_ctx* c, sr_stats* out) {
     if (!c || !out) return SR_ERR_ARG;
     *out = c->stats;

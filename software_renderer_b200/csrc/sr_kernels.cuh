@@ -966,6 +966,87 @@ __global__ void __launch_bounds__(256) k_points_resolve(const int* __restrict__ 
     if (depth_out) depth_out[o] = __int_as_float(0x7f800000);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Legacy 2-D immediate-mode API (R:376-465).  One kernel per command, launched in command order on one stream.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int sgn_i(int v) { return (v > 0) - (v < 0); }
+
+// draw(rect:) R:376-383: rect.w drives y, rect.h drives x (as written); unchecked stores.
+__global__ void __launch_bounds__(256) k2d_rect(unsigned* __restrict__ img, int W, int x0, int y0, int w, int h, unsigned color) {
+    const int nx = abs(h), ny = abs(w);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nx * ny) return;
+    const int iy = t / nx, ix = t - iy * nx;
+    img[(size_t)(y0 + iy * sgn_i(w)) * W + (x0 + ix * sgn_i(h))] = color;
+}
+
+// draw(circle:) R:385-403: length = sqrt(x*x + y*y) and smoothstep = t*t*(3 - 2t), every operation rounded separately
+// (the definition the test oracle shares, see include/sr_cuda.h); only the blue channel carries d.
+__global__ void __launch_bounds__(256) k2d_circle(unsigned* __restrict__ img, int W, int cx, int cy, int ri) {
+    const int n = 2 * abs(ri);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * n) return;
+    const int iy = t / n, ix = t - iy * n;
+    const int dy = -ri + iy * sgn_i(ri), dx = -ri + ix * sgn_i(ri);
+    const float r = __int2float_rn(ri);
+    const float px = __fadd_rn(__int2float_rn(dx), 0.5f), py = __fadd_rn(__int2float_rn(dy), 0.5f);
+    const float l = __fsqrt_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)));
+    float d;
+    if (l < __fsub_rn(r, 2.0f)) {
+        d = 1.0f;
+    } else {
+        const float e0 = __fadd_rn(r, 2.0f), e1 = __fsub_rn(r, 2.0f);
+        const float u = fminf(fmaxf(__fdiv_rn(__fsub_rn(l, e0), __fsub_rn(e1, e0)), 0.0f), 1.0f);
+        d = fminf(fmaxf(__fmul_rn(__fmul_rn(u, u), __fsub_rn(3.0f, __fmul_rn(2.0f, u))), 0.0f), 1.0f);
+    }
+    const unsigned b = (unsigned)__float2int_rz(__fmul_rn(fminf(fmaxf(d, 0.0f), 1.0f), 255.0f));
+    img[(size_t)(cy + dy) * W + (cx + dx)] = b | 0xFF000000u;              // .floats(b: d, g: 0, r: 0, a: 1)
+}
+
+// draw(line:) R:405-419: the float accumulation x += xStep is sequential by definition: one thread walks the line.
+__global__ void k2d_line(unsigned* __restrict__ img, int W, int H, int x0, int y0, int x1, int y1, unsigned color) {
+    if (blockIdx.x | threadIdx.x) return;
+    const int dx = x1 - x0, dy = y1 - y0;
+    const int steps = max(abs(dx), abs(dy));
+    const float xs = __fdiv_rn(__int2float_rn(dx), __int2float_rn(steps)), ys = __fdiv_rn(__int2float_rn(dy), __int2float_rn(steps));
+    float x = __int2float_rn(x0), y = __int2float_rn(y0);
+    for (int s = 0; s < steps; ++s) {
+        const long long px = (long long)roundf(x), py = (long long)roundf(y);   // .rounded(): to nearest, ties away from zero
+        if (px >= 0 && px < W && py >= 0 && py < H) img[(size_t)py * W + (size_t)px] = color;   // bounds-checked setter R:30-36
+        x = __fadd_rn(x, xs);
+        y = __fadd_rn(y, ys);
+    }
+}
+
+// draw(triangle:with:in:) R:421-465: one thread per row of the span rule; colour = barycentric weights.
+__global__ void __launch_bounds__(128) k2d_triangle(unsigned* __restrict__ img, int W, int H, int ax, int ay, int bx, int by, int cx, int cy) {
+    // stable sort on INT y (R:422), strict <
+    int sx[3] = {ax, bx, cx}, sy[3] = {ay, by, cy};
+#pragma unroll
+    for (int i = 1; i < 3; ++i)
+        for (int j = i; j > 0 && sy[j] < sy[j - 1]; --j) {
+            int t = sy[j]; sy[j] = sy[j - 1]; sy[j - 1] = t;
+            t = sx[j]; sx[j] = sx[j - 1]; sx[j - 1] = t;
+        }
+    const SortedTri s = {sx[0], sy[0], sx[1], sy[1], sx[2], sy[2]};
+    const long long row = (long long)max(s.y0, 0) + (long long)blockIdx.x * blockDim.x + threadIdx.x;   // rows outside the image store nothing
+    if (row > (long long)min(s.y2, H - 1)) return;
+    const int y = (int)row;
+    int l, r;
+    span_row(s, y, l, r);
+    l = max(l, 0);
+    r = min(r, W - 1);
+    const BaryT bt = bary_setup(ax, ay, bx, by, cx, cy);
+    for (int x = l; x <= r; ++x) {
+        const float3 w = bary_weights(bt, x, y);
+        // (ac*ws.x + bc*ws.y + cc*ws.z) * a with unit colours, a = 1 (R:448-452)
+        const float cr = __fmul_rn(__fadd_rn(__fadd_rn(__fmul_rn(w.x, 1.0f), __fmul_rn(w.y, 0.0f)), __fmul_rn(w.z, 0.0f)), 1.0f);
+        const float cg = __fmul_rn(__fadd_rn(__fadd_rn(__fmul_rn(w.x, 0.0f), __fmul_rn(w.y, 1.0f)), __fmul_rn(w.z, 0.0f)), 1.0f);
+        const float cb = __fmul_rn(__fadd_rn(__fadd_rn(__fmul_rn(w.x, 0.0f), __fmul_rn(w.y, 0.0f)), __fmul_rn(w.z, 1.0f)), 1.0f);
+        img[(size_t)y * W + x] = pack_bgra(cr, cg, cb);
+    }
+}
+
 __global__ void k_fill_u64(unsigned long long* __restrict__ p, size_t n, unsigned long long value) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = value;

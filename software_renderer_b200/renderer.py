@@ -28,6 +28,7 @@ FLAG_NO_DEPTH_OUT = 1 << 1
 ABI_SYMBOLS = (
     "sr_version", "sr_create", "sr_destroy", "sr_last_error", "sr_set_mesh", "sr_render", "sr_render_pass",
     "sr_render_batch", "sr_render_device", "sr_sync", "sr_get_stats", "sr_get_kernel_times", "sr_set_profiling",
+    "sr_draw2d",
 )
 
 
@@ -40,6 +41,46 @@ class PrimitiveType(enum.IntEnum):
     @property
     def vertices_count(self) -> int:
         return 2 if self is PrimitiveType.line else 3
+
+
+class Cmd2D(ctypes.Structure):
+    """sr_cmd2d: one command of the legacy 2-D immediate-mode API (Renderer.swift:376-465)."""
+    _fields_ = [("kind", ctypes.c_int32), ("p", ctypes.c_int32 * 6), ("color", ctypes.c_uint8 * 4)]
+
+    RECT, CIRCLE, LINE, TRIANGLE = 0, 1, 2, 3
+
+    @classmethod
+    def make(cls, kind, params, color=(0, 0, 0, 0)):
+        c = cls()
+        c.kind = kind
+        for k, v in enumerate(params):
+            c.p[k] = int(v)
+        for k, v in enumerate(color):
+            c.color[k] = int(v)
+        return c
+
+    @classmethod
+    def rect(cls, x, y, w, h, color):            # draw(rect:with:in:)  — note: w drives y and h drives x (R:378-379)
+        return cls.make(cls.RECT, (x, y, w, h), color)
+
+    @classmethod
+    def circle(cls, x, y, r):                    # draw(circle:with:in:) — the colour argument is ignored by the reference
+        return cls.make(cls.CIRCLE, (x, y, r))
+
+    @classmethod
+    def line(cls, x0, y0, x1, y1, color):        # draw(line:with:in:)
+        return cls.make(cls.LINE, (x0, y0, x1, y1), color)
+
+    @classmethod
+    def triangle(cls, a, b, c):                  # draw(triangle:with:in:) — colour = barycentric weights
+        return cls.make(cls.TRIANGLE, (a[0], a[1], b[0], b[1], c[0], c[1]))
+
+
+def pack_cmds(cmds):
+    arr = (Cmd2D * max(len(cmds), 1))()
+    for k, c in enumerate(cmds):
+        arr[k] = c
+    return arr
 
 
 class SrStats(ctypes.Structure):
@@ -105,6 +146,8 @@ def load_library():
     L.sr_get_kernel_times.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_float), i32]
     L.sr_set_profiling.restype = i32
     L.sr_set_profiling.argtypes = [vp, i32]
+    L.sr_draw2d.restype = i32
+    L.sr_draw2d.argtypes = [vp, vp, sz, i32, i32, vp]
     _lib = L
     return L
 
@@ -244,6 +287,13 @@ class CudaRenderer:
 
     def sync(self):
         self._check(self._lib.sr_sync(self._ctx))
+
+    def draw2d(self, cmds, image: np.ndarray):
+        """Runs legacy 2-D commands (Cmd2D.rect/circle/line/triangle) in order on a (H, W, 4) BGRA8 image, in place."""
+        assert image.dtype == np.uint8 and image.ndim == 3 and image.shape[2] == 4 and image.flags.c_contiguous
+        arr = pack_cmds(cmds)
+        self._check(self._lib.sr_draw2d(self._ctx, arr, len(cmds), image.shape[1], image.shape[0], image.ctypes.data))
+        return image
 
     # -- introspection -----------------------------------------------------------------------------------------
     def stats(self) -> dict:
