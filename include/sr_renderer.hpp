@@ -9,6 +9,7 @@
 // std::runtime_error / returns the count of skipped primitives; it never falls back to the CPU.
 #pragma once
 #include <cstdint>
+#include <initializer_list>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -79,10 +80,24 @@ public:
         return st.domain_skipped;
     }
 
+    // legacy 2-D immediate API (Renderer.swift:376-465): draw(rect:), draw(circle:), draw(line:), draw(triangle:with:in:)
+    void drawRect(int x, int y, int w, int h, Pixel color, const ColorImage& image) { draw2d(SR_2D_RECT, {x, y, w, h, 0, 0}, color, image); }
+    void drawCircle(int x, int y, int r, const ColorImage& image) { draw2d(SR_2D_CIRCLE, {x, y, r, 0, 0, 0}, Pixel{}, image); }
+    void drawLine(int x0, int y0, int x1, int y1, Pixel color, const ColorImage& image) { draw2d(SR_2D_LINE, {x0, y0, x1, y1, 0, 0}, color, image); }
+    void drawTriangle(int ax, int ay, int bx, int by, int cx, int cy, const ColorImage& image) { draw2d(SR_2D_TRIANGLE, {ax, ay, bx, by, cx, cy}, Pixel{}, image); }
+
     sr_stats stats() const { sr_stats st{}; sr_get_stats(ctx_, &st); return st; }
     sr_ctx* raw() const { return ctx_; }
 
 private:
+    void draw2d(int kind, std::initializer_list<int> p, Pixel color, const ColorImage& image) {
+        sr_cmd2d cmd{};
+        cmd.kind = kind;
+        int k = 0;
+        for (int v : p) cmd.p[k++] = v;
+        cmd.color[0] = color.b; cmd.color[1] = color.g; cmd.color[2] = color.r; cmd.color[3] = color.a;
+        check(sr_draw2d(ctx_, &cmd, 1, image.width, image.height, reinterpret_cast<uint8_t*>(image.pointer)));
+    }
     void check(int rc) const {
         if (rc != SR_OK) throw std::runtime_error(std::string("libsr_cuda: ") + sr_last_error(ctx_) + " (" + std::to_string(rc) + ")");
     }

@@ -46,6 +46,13 @@ public struct RenderPass {
     }
 }
 
+/// Renderer.swift:51-70 — shapes of the legacy 2-D immediate API
+public struct Rect { public var x: Int, y: Int, w: Int, h: Int; public init(x: Int, y: Int, w: Int, h: Int) { self.x = x; self.y = y; self.w = w; self.h = h } }
+public struct Circle { public var x: Int, y: Int, r: Int; public init(x: Int, y: Int, r: Int) { self.x = x; self.y = y; self.r = r } }
+public struct Line { public var x0: Int, y0: Int, x1: Int, y1: Int; public init(x0: Int, y0: Int, x1: Int, y1: Int) { self.x0 = x0; self.y0 = y0; self.x1 = x1; self.y1 = y1 } }
+/// Renderer.swift:76-80
+public struct Triangle { public var a: vector_long2, b: vector_long2, c: vector_long2; public init(a: vector_long2, b: vector_long2, c: vector_long2) { self.a = a; self.b = b; self.c = c } }
+
 public enum CudaRendererError: Error { case create(Int32), render(Int32, String) }
 
 public final class CudaRenderer {
@@ -94,5 +101,29 @@ public final class CudaRenderer {
         sr_get_stats(ctx, &st)
         lastDomainSkips = st.domain_skipped
         precondition(rc == 0 || rc == SR_ERR_DOMAIN.rawValue, String(cString: sr_last_error(ctx)))
+    }
+
+    // MARK: legacy 2-D immediate API (Renderer.swift:376-465) — same signatures, one sr_draw2d command each
+
+    private func draw2d(_ kind: Int32, _ p: [Int], _ color: Pixel, in image: ColorImage) {
+        var cmd = sr_cmd2d()
+        cmd.kind = kind
+        withUnsafeMutableBytes(of: &cmd.p) { b in for (k, v) in p.enumerated() { b.storeBytes(of: Int32(truncatingIfNeeded: v), toByteOffset: 4 * k, as: Int32.self) } }
+        cmd.color = (color.b, color.g, color.r, color.a)
+        let rc = sr_draw2d(ctx, &cmd, 1, Int32(image.width), Int32(image.height),
+                           UnsafeMutableRawPointer(image.pointer).assumingMemoryBound(to: UInt8.self))
+        precondition(rc == 0, String(cString: sr_last_error(ctx)))   // the reference corrupts memory / traps here
+    }
+    public func draw(rect: Rect, with color: Pixel, in image: ColorImage) {
+        draw2d(Int32(SR_2D_RECT.rawValue), [rect.x, rect.y, rect.w, rect.h], color, in: image)
+    }
+    public func draw(circle: Circle, with color: Pixel, in image: ColorImage) {
+        draw2d(Int32(SR_2D_CIRCLE.rawValue), [circle.x, circle.y, circle.r], color, in: image)
+    }
+    public func draw(line: Line, with color: Pixel, in image: ColorImage) {
+        draw2d(Int32(SR_2D_LINE.rawValue), [line.x0, line.y0, line.x1, line.y1], color, in: image)
+    }
+    public func draw(triangle: Triangle, with color: Pixel, in image: ColorImage) {
+        draw2d(Int32(SR_2D_TRIANGLE.rawValue), [triangle.a.x, triangle.a.y, triangle.b.x, triangle.b.y, triangle.c.x, triangle.c.y], color, in: image)
     }
 }

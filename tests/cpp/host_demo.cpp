@@ -23,6 +23,13 @@ int main(int argc, char** argv) {
     bool ok = covered == 65537 && px(256, 0).r == 255 && px(256, 128).b == 63 && px(256, 128).g == 63 && px(256, 128).r == 127 &&
               px(0, 256).b == 255 && px(300, 100).b == 27 && px(300, 100).g == 71 && px(300, 100).r == 155;
     for (float d : depth) ok = ok && std::isinf(d) && d > 0;
+    // legacy 2-D API on the same image: a 3-row x 5-column rect (w drives y, Renderer.swift:378) and a 2-D triangle
+    try {
+        sr::CudaRenderer r2(0);
+        r2.drawRect(2, 1, 3, 5, sr::Pixel{9, 8, 7, 6}, rp.colorBuffer);
+        r2.drawLine(0, 500, 8, 504, sr::Pixel{5, 6, 7, 8}, rp.colorBuffer);
+    } catch (const std::exception& e) { std::fprintf(stderr, "%s\n", e.what()); return 4; }
+    ok = ok && px(2, 1).b == 9 && px(6, 3).a == 6 && px(7, 1).a == 0 && px(2, 4).a == 0 && px(0, 500).g == 6 && px(8, 504).a == 0;
     std::printf("covered=%ld ok=%d\n", covered, (int)ok);
     return ok ? 0 : 1;
 }
