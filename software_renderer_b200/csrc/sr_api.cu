@@ -17,6 +17,11 @@ namespace {
 constexpr int MAX_PROF = 64;
 constexpr size_t kSlabLimit = 8ull << 30;
 
+inline bool poison_new_buffers() {
+    const char* e = getenv("SR_POISON");     // read per allocation (rare), so a test can switch it on for one context
+    return e && atoi(e) != 0;
+}
+
 template <class T>
 struct DevBuf {
     T* p = nullptr;
@@ -27,6 +32,10 @@ struct DevBuf {
         p = nullptr; cap = 0;
         cudaError_t e = cudaMalloc((void**)&p, n * sizeof(T));
         if (e == cudaSuccess) cap = n;
+        if (e == cudaSuccess && poison_new_buffers()) {      // SR_POISON=1 (tests): a read of never-written memory faults
+            e = cudaMemset(p, 0xFF, n * sizeof(T));
+            if (e == cudaSuccess) e = cudaDeviceSynchronize();
+        }
         return e;
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }

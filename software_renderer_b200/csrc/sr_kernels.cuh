@@ -577,8 +577,11 @@ __global__ void __launch_bounds__(256) k_bin_fill(const TriRec* __restrict__ rec
                         const SortedTri st = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                         const int tx = r.tx0 + qx, ty = r.ty0 + qy;
                         const int ya = max(max(ty * TILE, t.y0), 0), yb = min(min(ty * TILE + TILE - 1, t.y2), fp.height - 1);
-                        keep = rect_touched(st, EdgeRcp{edge_rcp(t.y1 - t.y0), edge_rcp(t.y2 - t.y1), edge_rcp(t.y2 - t.y0)},
-                                            tx * TILE, min(tx * TILE + TILE - 1, fp.width - 1), ya, yb);
+                        // tile COLUMNS of the band's extent, exactly as k_setup counted them (a partial last column
+                        // is counted even when the extent starts right of the image): count == fill, no list gaps
+                        int mn, mx;
+                        row_band_extent(st, EdgeRcp{edge_rcp(t.y1 - t.y0), edge_rcp(t.y2 - t.y1), edge_rcp(t.y2 - t.y0)}, ya, yb, mn, mx);
+                        keep = (mn >> TILE_SHIFT) <= tx && tx <= (mx >> TILE_SHIFT);
                     }
                     if (keep)
                         pos[u] = atomicAdd(&cursor[(size_t)tile * NCHUNK + cs], 1u);

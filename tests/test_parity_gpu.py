@@ -428,3 +428,31 @@ def test_depth_bounds_never_change_the_image(case):
             assert s["depth_culled"] > 0.5 * s["tile_pairs"]
     finally:
         r.close()
+
+
+def test_compact_lists_right_edge_columns():
+    """Compact tile lists: the counting pass (k_setup) and the fill pass (k_bin_fill) must agree tile by tile, or a
+    list has a gap of never-written entries.  Triangles whose rows leave the image through a partial last tile
+    column (width not a multiple of 16) are the case where the two passes once disagreed."""
+    import os
+    env = {"SR_SLAB": "0", "SR_POISON": "1"}
+    os.environ.update(env)
+    try:
+        r = srb.CudaRenderer(0)
+        W, H = 690, 400
+        rng = np.random.default_rng(5)
+        tris = []
+        for _ in range(200):
+            x0 = rng.uniform(660, 689); y0 = rng.uniform(0, 200)
+            tris += [(x0, y0), (x0 + rng.uniform(100, 400), y0 + rng.uniform(0, 30)), (x0 + rng.uniform(100, 400), y0 + rng.uniform(100, 300))]
+        px = np.array(tris)
+        xyz = np.stack([px[:, 0] / W * 2 - 1, 1 - px[:, 1] / H * 2, rng.uniform(0, 1, len(px))], 1).astype(np.float32)
+        v = S.pack_vertices(xyz, rng.uniform(0, 1, size=(len(px), 3)).astype(np.float32))
+        i = np.arange(len(px), dtype=np.int64)
+        for dt in (False, True):
+            assert_same(r, v, i, I4, W, H, depth_test=dt)
+        assert r.stats()["binned_tris"] > 0
+        r.close()
+    finally:
+        for k in env:
+            del os.environ[k]
