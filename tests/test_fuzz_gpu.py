@@ -106,3 +106,64 @@ def test_fuzz_all_policies(policy, cases):
     finally:
         for k in env:
             del os.environ[k]
+
+
+def _view(rng, scale):
+    """rotation * scale, pushed back along z, then the w = z + 1 projection of App.swift:176-181."""
+    q = rng.normal(size=4)
+    q /= np.linalg.norm(q)
+    w, x, y, z = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                  [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                  [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    m = np.eye(4)
+    m[:3, :3] = R * scale
+    m[2, 3] = 1.5
+    p = np.eye(4)
+    p[3, 2] = 1.0
+    return (p @ m).astype(np.float32)
+
+
+@pytest.fixture(scope="module")
+def view_cases():
+    """One shared-vertex mesh seen from 14 cameras whose zoom spans sub-pixel triangles to a few screen-filling ones
+    (some corners behind the eye: negative w, still finite).  Consecutive views want different host policies."""
+    rng = np.random.default_rng(0xCA3E)
+    v, i = S.cube_sphere(40)
+    W, H = 333, 251
+    views = np.stack([_view(rng, s) for s in np.exp(rng.uniform(np.log(0.1), np.log(8.0), size=14))])
+    want = {}
+    for dt in (False, True):
+        outs = [O.render(v, i, m, W, H, flags=O.DEPTH_LESS if dt else 0) for m in views]
+        want[dt] = outs
+    return v, i, views, W, H, want
+
+
+@pytest.mark.parametrize("policy", POLICIES, ids=lambda p: ",".join(f"{k}={v}" for k, v in p.items()) or "default")
+def test_fuzz_views_all_policies(policy, view_cases):
+    v, i, views, W, H, want = view_cases
+    env = dict(policy, SR_POISON="1")
+    os.environ.update(env)
+    try:
+        r = srb.CudaRenderer(0)
+        r.set_mesh(v, i)
+        for dt in (False, True):
+            r.depth_test = dt
+            for rounds in range(2):                      # second round starts from the policies the first one left
+                color = np.full((len(views), H, W, 4), 0x3C, np.uint8)
+                depth = np.full((len(views), H, W), -1.0, np.float32)
+                skipped = sum(o[3]["domain_skipped"] for o in want[dt])
+                try:
+                    r.render_views(views, W, H, color_out=color, depth_out=depth)
+                    assert skipped == 0
+                except srb.DomainError:
+                    assert skipped > 0
+                for k, (rc, rc_c, rc_d, _) in enumerate(want[dt]):
+                    bad = (color[k] != rc_c).any(-1)
+                    assert not bad.any(), f"view {k} depth={dt} round {rounds}: {int(bad.sum())} colour pixels differ"
+                    assert np.array_equal(depth[k].view(np.uint32), rc_d.view(np.uint32)), f"view {k} depth={dt}: depth differs"
+        r.depth_test = False
+        r.close()
+    finally:
+        for k in env:
+            del os.environ[k]
