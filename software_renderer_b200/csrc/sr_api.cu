@@ -69,6 +69,7 @@ struct sr_ctx {
     DevBuf<unsigned> ticket;
     unsigned ticket_base = 0, epoch = 0;
     DevBuf<unsigned> tile_done;             // frame stamp of tiles retired early (batched mode)
+    DevBuf<unsigned> done_bits;             // the same as a bitmap (one bit per tile), all zero between frames
     unsigned frame_epoch = 0;
     // adaptive policy (depth off): index-descending batches pay off when most tile-list entries are never read
     bool batched_mode = false;
@@ -196,6 +197,11 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
         SR_CUDA(c, cudaMemsetAsync(c->tile_done.p, 0, tiles * sizeof(unsigned), st));
         c->frame_epoch = 0;
     }
+    const size_t nbits_words = div_up(div_up(W, TILE), 32) * div_up(H, TILE);
+    if (nbits_words > c->done_bits.cap) {
+        SR_CUDA(c, c->done_bits.reserve(nbits_words));
+        SR_CUDA(c, cudaMemsetAsync(c->done_bits.p, 0, nbits_words * sizeof(unsigned), st));
+    }
     const size_t nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
     if (nblocks > c->look.cap) {
         SR_CUDA(c, c->look.reserve(nblocks));
@@ -263,6 +269,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
         fp.epoch = ++c->frame_epoch;
         fp.batched = batched_frame ? 1 : 0;
+        fp.done_bits = c->done_bits.p;
+        fp.wpr = (int)div_up(fp.tiles_x, 32);
         fp.slab_cap = (c->slab_mode && (size_t)fp.ntiles * NCHUNK * c->slab_cap <= c->slab.cap) ? (int)c->slab_cap : 0;
         c->call_slab_cap = (unsigned)fp.slab_cap;
         c->last_ntiles = (size_t)fp.ntiles;
@@ -464,6 +472,19 @@ int finish_pending(sr_ctx* c) {
             if (rc) return rc;
         }
     }
+#ifdef SR_TIMELINE
+    for (size_t v = 0; v < nviews; ++v) {
+        const ViewStatus& s = c->h_status[v];
+        unsigned long long t0 = ~0ull;
+        for (int k = 0; k < 2 * MAX_BATCHES; ++k) if (s.tl_launch_inv[k]) t0 = std::min(t0, ~s.tl_launch_inv[k]);
+        fprintf(stderr, "view %zu:", v);
+        for (int k = 0; k < 2 * MAX_BATCHES; ++k)
+            if (s.tl_launch_inv[k])
+                fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
+                        (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
+        fprintf(stderr, "\n");
+    }
+#endif
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
     c->stats.gpu_ms = ms;
@@ -515,7 +536,7 @@ void sr_destroy(sr_ctx* c) {
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release(); c->slab.release(); c->ztri.release();
     c->counts.release(); c->cursor.release(); c->pairs.release(); c->vis32.release(); c->vis64.release();
-    c->look.release(); c->ticket.release(); c->status.release(); c->tile_done.release();
+    c->look.release(); c->ticket.release(); c->status.release(); c->tile_done.release(); c->done_bits.release();
     for (int i = 0; i < 2; ++i) {
         c->out_color[i].release(); c->out_depth[i].release();
         if (c->ev_render[i]) cudaEventDestroy(c->ev_render[i]);
@@ -605,8 +626,11 @@ int sr_render_device(sr_ctx* c, const float* transforms, size_t nviews, int prim
     const size_t npx = (size_t)W * H;
     uint8_t* color = (uint8_t*)color_dev;
     float* depth = (flags & SR_FLAG_NO_DEPTH_OUT) ? nullptr : (float*)depth_dev;
-    SR_CUDA(c, cudaMemsetAsync(c->status.p + first, 0, nviews * sizeof(ViewStatus), st));
-    if (!p.active) SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+    // one clear of every status slot when a group of accumulating calls starts (not one memset node per call)
+    if (!p.active) {
+        SR_CUDA(c, cudaMemsetAsync(c->status.p, 0, c->status.cap * sizeof(ViewStatus), st));
+        SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
+    }
     p.active = true;
     p.prim = prim; p.width = W; p.height = H; p.flags = flags; p.stream = st;
     for (size_t i = 0; i < nviews; ++i) {
@@ -677,6 +701,19 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
             if (want_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[0].p, npx * sizeof(float), cudaMemcpyDeviceToHost, st));
         }
     }
+#ifdef SR_TIMELINE
+    for (size_t v = 0; v < nviews; ++v) {
+        const ViewStatus& s = c->h_status[v];
+        unsigned long long t0 = ~0ull;
+        for (int k = 0; k < 2 * MAX_BATCHES; ++k) if (s.tl_launch_inv[k]) t0 = std::min(t0, ~s.tl_launch_inv[k]);
+        fprintf(stderr, "view %zu:", v);
+        for (int k = 0; k < 2 * MAX_BATCHES; ++k)
+            if (s.tl_launch_inv[k])
+                fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
+                        (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
+        fprintf(stderr, "\n");
+    }
+#endif
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
     c->stats.gpu_ms = ms;

@@ -48,7 +48,22 @@ struct ViewStatus {
     unsigned open_after_first;          // batched mode: tiles still open after the first batch
     unsigned zlo_inv, zhi;              // depth mode: ~min / max of depth_ord(lower bound) over binned triangles
     unsigned long long pairs_culled;    // depth mode: records rejected by their depth bound or never read
+#ifdef SR_TIMELINE
+    // debug build: %globaltimer stamps per launch slot (2 * batch + {0 k_setup, 1 k_tile}): first CTA started,
+    // first CTA past the grid dependency, last CTA finished.  Gives the overlapped timeline of a frame.
+    unsigned long long tl_launch_inv[2 * MAX_BATCHES], tl_go_inv[2 * MAX_BATCHES], tl_end[2 * MAX_BATCHES];
+#endif
 };
+#ifdef SR_TIMELINE
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TL_BEGIN(st, slot) do { if (threadIdx.x == 0) atomicMax(&(st)->tl_launch_inv[slot], ~gtime()); } while (0)
+#define TL_GO(st, slot)    do { if (threadIdx.x == 0) atomicMax(&(st)->tl_go_inv[slot], ~gtime()); } while (0)
+#define TL_END(st, slot)   do { if (threadIdx.x == 0) atomicMax(&(st)->tl_end[slot], gtime()); } while (0)
+#else
+#define TL_BEGIN(st, slot) do {} while (0)
+#define TL_GO(st, slot)    do {} while (0)
+#define TL_END(st, slot)   do {} while (0)
+#endif
 
 // Bin-list record of a large triangle (32 B = one sector): corners SORTED as R:271 leaves them and the sort
 // permutation (to get back to the original a,b,c order of R:251).  Slab lists hold the records themselves (the tile
@@ -135,7 +150,24 @@ struct FrameParams {
                               //   bound is >= zthr[c-1] (chunk 0: everything else), so lists run front to back
     int nobin;                // 1: speculative frame without binning kernels (the previous frame had no large
                               //    triangle); a large triangle is only counted and the host re-runs the frame
+    unsigned* done_bits;      // batched frames: one bit per retired tile, `wpr` words per tile row; all zero between
+    int wpr;                  //   frames (set by k_tile when it retires a tile, cleared by the final batch's k_tile)
 };
+
+// Retired-tile bitmap (batched frames).  It is constant while k_setup runs, so the loads may take the read-only path.
+__device__ __forceinline__ bool tile_retired(const FrameParams& fp, int tx, int ty) {
+    return (__ldg(&fp.done_bits[ty * fp.wpr + (tx >> 5)]) >> (tx & 31)) & 1u;
+}
+// any tile of row `ty`, columns [txa, txb], still open?
+__device__ __forceinline__ bool row_has_open(const FrameParams& fp, int ty, int txa, int txb) {
+    const unsigned* row = fp.done_bits + ty * fp.wpr;
+    for (int w = txa >> 5; w <= (txb >> 5); ++w) {
+        const int lo = max(txa - (w << 5), 0), hi = min(txb - (w << 5), 31);
+        const unsigned mask = (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
+        if (~__ldg(&row[w]) & mask) return true;
+    }
+    return false;
+}
 struct BatchParams {
     int lo, hi;               // primitive range [lo, hi) of this batch
     int chunk_shift;          // chunk = (prim - lo) >> chunk_shift  (< NCHUNK)
@@ -196,14 +228,17 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
                                                float4* __restrict__ ztri, const unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
+    TL_BEGIN(status, 2 * bp.index);
     pdl_wait();
+    TL_GO(status, 2 * bp.index);
     __shared__ StagedTri s_tri[256];
     __shared__ StagedRect s_rect[BIN ? 256 : 1];
     __shared__ BaryT s_bt[DEPTH ? 256 : 1];
     __shared__ float s_z[DEPTH ? 256 : 1][3];
     __shared__ unsigned s_nsmall;
 
-    if (fp.batched && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
+    const bool late = fp.batched && bp.index > 0;                   // only later batches can meet retired tiles
+    if (late && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
     if (fp.batched && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&status->batches_run, 1u);
     if (threadIdx.x == 0) s_nsmall = 0;
     __syncthreads();
@@ -262,7 +297,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
                 if (DEPTH) bt = bary_setup(ax, ay, bx, by, cx, cy);
                 auto plot = [&](int x, int y) {
                     if ((unsigned)x >= (unsigned)fp.width || (unsigned)y >= (unsigned)fp.height) return;   // R:246-250
-                    if (fp.batched && tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] == fp.epoch) return;
+                    if (late && tile_retired(fp, x >> TILE_SHIFT, y >> TILE_SHIFT)) return;
                     const size_t o = (size_t)y * fp.width + x;
                     if (DEPTH) {
                         const float d = blend3(a.z, b.z, c.z, bary_weights(bt, x, y));
@@ -279,12 +314,12 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
         }
     }
     int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
-    if (fp.batched && (small || large)) {
-        // retire triangles whose tiles are all done (cheap test for footprints of at most 2x2 tiles)
-        if (tx1 - tx0 <= 1 && ty1 - ty0 <= 1) {
+    if (late && (small || large)) {
+        // retire triangles whose bbox tiles are all done: a few words of the retired-tile bitmap per tile row (taller
+        // footprints are tested row by row where their tile-row items are processed)
+        if (ty1 - ty0 < 8) {
             bool open = false;
-            for (int ty = ty0; ty <= ty1; ++ty)
-                for (int tx = tx0; tx <= tx1; ++tx) open |= tile_done[ty * fp.tiles_x + tx] != fp.epoch;
+            for (int ty = ty0; ty <= ty1 && !open; ++ty) open = row_has_open(fp, ty, tx0, tx1);
             if (!open) small = large = false;
         }
     }
@@ -371,12 +406,13 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
         warp_balance(large ? (ty1 - ty0 + 1) : 0, [&](int src, int item) {
             const StagedRect r = s_rect[wbase + src];
             const int cs = r.w >> 16, ty = r.ty0 + item;
+            if (late && !row_has_open(fp, ty, r.tx0, r.tx0 + (r.w & 0x7fff) - 1)) return;
             int ta, tb;
             tile_row_range(src, r, ty, ta, tb);
             const unsigned seg0 = (unsigned)(ty * fp.tiles_x) * NCHUNK + cs;
             if (!fp.slab_cap) {
                 for (int tx = ta; tx <= tb; ++tx)
-                    if (!(fp.batched && tile_done[ty * fp.tiles_x + tx] == fp.epoch)) atomicAdd(&counts[seg0 + tx * NCHUNK], 1u);
+                    if (!(late && tile_retired(fp, tx, ty))) atomicAdd(&counts[seg0 + tx * NCHUNK], 1u);
                 return;
             }
             for (int tx = ta; tx <= tb; tx += 4) {
@@ -384,7 +420,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     pos[u] = 0xffffffffu;
-                    if (tx + u <= tb && !(fp.batched && tile_done[ty * fp.tiles_x + tx + u] == fp.epoch))
+                    if (tx + u <= tb && !(late && tile_retired(fp, tx + u, ty)))
                         pos[u] = atomicAdd(&counts[seg0 + (tx + u) * NCHUNK], 1u);
                 }
 #pragma unroll
@@ -414,7 +450,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
             l = max(l, 0);
             r = min(r, fp.width - 1);
             for (int x = l; x <= r; ++x) {                       // R:281
-                if (fp.batched && tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] == fp.epoch) continue;
+                if (late && tile_retired(fp, x >> TILE_SHIFT, y >> TILE_SHIFT)) continue;
                 const size_t o = (size_t)y * fp.width + x;
                 if (DEPTH) {
                     const float3 w = bary_weights(s_bt[wbase + src], x, y);
@@ -428,6 +464,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
     }
     __syncthreads();
     if (threadIdx.x == 0 && s_nsmall) atomicAdd(&status->n_small, s_nsmall);
+    TL_END(status, 2 * bp.index);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -634,7 +671,9 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                                               const unsigned* __restrict__ pairs, unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
                                               unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status,
                                               unsigned* __restrict__ color_out, float* __restrict__ depth_out) {
+    TL_BEGIN(status, 2 * bp.index + 1);
     pdl_wait();
+    TL_GO(status, 2 * bp.index + 1);
     __shared__ __align__(16) unsigned short s_mask[TILE][TILE_BATCH];
     __shared__ unsigned s_prim[TILE_BATCH];
     __shared__ TriRec s_rec[2][TILE_BATCH];
@@ -653,7 +692,9 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
 #pragma unroll
         for (int q = 0; q < NCHUNK - 1; ++q) if (tid == q) s_zord[q] = depth_ord(fp.zthr[q]);
     }
-    if (late && status->tiles_done >= (unsigned)fp.ntiles) return;
+    if (fp.batched && bp.final_batch)       // nothing reads the retired-tile bitmap any more: leave it zero for the next frame
+        for (int w = blockIdx.x * blockDim.x + tid; w < fp.wpr * fp.tiles_y; w += gridDim.x * blockDim.x) fp.done_bits[w] = 0u;
+    if (late && status->tiles_done >= (unsigned)fp.ntiles) { TL_END(status, 2 * bp.index + 1); return; }
 
     // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA launches
     for (int tile = blockIdx.x; tile < fp.ntiles; tile += gridDim.x) {
@@ -860,7 +901,11 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     if (fp.batched && !bp.final_batch) {
         // a pixel covered by this or an earlier batch cannot be changed by later (lower-index) batches
         shade_now = __syncthreads_and(!inside || v != 0u) != 0;
-        if (shade_now && tid == 0) { tile_done[tile] = fp.epoch; atomicAdd(&status->tiles_done, 1u); }
+        if (shade_now && tid == 0) {
+            tile_done[tile] = fp.epoch;
+            atomicOr(&fp.done_bits[ty * fp.wpr + (tx >> 5)], 1u << (tx & 31));
+            atomicAdd(&status->tiles_done, 1u);
+        }
     }
     if (!inside) continue;
     if (!shade_now) { if (v != v_in) vis32[o] = v; continue; }      // park for the next batch
@@ -873,6 +918,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     color_out[o] = bgra;
     if (depth_out) depth_out[o] = depth;
     }   // tile loop
+    TL_END(status, 2 * bp.index + 1);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
