@@ -251,17 +251,19 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
     int ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, y0 = 0, y1 = -1, xmin = 0, xmax = -1;
     unsigned perm = 0;
     float za = 0.0f, zb = 0.0f, zc = 0.0f;
+    float fx[3] = {0.0f, 0.0f, 0.0f}, fy[3] = {0.0f, 0.0f, 0.0f};      // XFORM: screen corners, stored once the triangle survives
     if (valid) {
         const int i0 = idx[3 * (size_t)prim], i1 = idx[3 * (size_t)prim + 1], i2 = idx[3 * (size_t)prim + 2];
         float4 a, b, c;
         if (XFORM) {
+            // depth is off in every frame that transforms here, so z_ndc is never read; the corners are stored
+            // further down, and only for triangles that can still win a pixel
             auto corner = [&](int i) {
-                const float3 t = transform_to_screen(xf.M, xf.pos[3 * (size_t)i], xf.pos[3 * (size_t)i + 1], xf.pos[3 * (size_t)i + 2], xf.fw, xf.fh);
-                const float4 r = make_float4(t.x, t.y, t.z, 0.0f);
-                sv[i] = r;                                  // shared vertices: every writer stores the same bits
-                return r;
+                const float3 t = transform_to_screen<false>(xf.M, xf.pos[3 * (size_t)i], xf.pos[3 * (size_t)i + 1], xf.pos[3 * (size_t)i + 2], xf.fw, xf.fh);
+                return make_float4(t.x, t.y, 0.0f, 0.0f);
             };
             a = corner(i0); b = corner(i1); c = corner(i2);
+            fx[0] = a.x; fy[0] = a.y; fx[1] = b.x; fy[1] = b.y; fx[2] = c.x; fy[2] = c.y;
         } else {
             a = __ldg(&sv[i0]); b = __ldg(&sv[i1]); c = __ldg(&sv[i2]);     // read-only path (sv is written only under XFORM)
         }
@@ -322,6 +324,12 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int
             for (int ty = ty0; ty <= ty1 && !open; ++ty) open = row_has_open(fp, ty, tx0, tx1);
             if (!open) small = large = false;
         }
+    }
+    if (XFORM && (tiny || small || large)) {     // shading reads the corners of the winner (shared vertices: every
+        const int i0 = idx[3 * (size_t)prim], i1 = idx[3 * (size_t)prim + 1], i2 = idx[3 * (size_t)prim + 2];   // writer stores the same bits)
+        sv[i0] = make_float4(fx[0], fy[0], 0.0f, 0.0f);
+        sv[i1] = make_float4(fx[1], fy[1], 0.0f, 0.0f);
+        sv[i2] = make_float4(fx[2], fy[2], 0.0f, 0.0f);
     }
     // warp-aggregated counters and bin-list append
     const unsigned m_skip = __ballot_sync(0xffffffffu, skipped);

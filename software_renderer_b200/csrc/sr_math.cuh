@@ -14,10 +14,13 @@ struct Mat4 { float m[16]; };  // column-major, like matrix_float4x4 (R:199)
 
 // Vertex.apply (R:159-163) + convertedToScreen (R:165-172).  Returns (sx, sy, z_ndc).
 // matrix * float4 is column accumulation with separately rounded * and + (the definition shared with oracle/).
+// WITH_Z = false leaves z_ndc out (returned as 0): with the depth test off nothing reads it.
+template <bool WITH_Z = true>
 __device__ __forceinline__ float3 transform_to_screen(const Mat4& M, float x, float y, float z, float fw, float fh) {
     float v[4];
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
+        if (!WITH_Z && r == 2) { v[r] = 0.0f; continue; }
         float acc = __fmul_rn(M.m[r], x);
         acc = __fadd_rn(acc, __fmul_rn(M.m[4 + r], y));
         acc = __fadd_rn(acc, __fmul_rn(M.m[8 + r], z));
@@ -26,7 +29,7 @@ __device__ __forceinline__ float3 transform_to_screen(const Mat4& M, float x, fl
     }
     float nx = __fdiv_rn(v[0], v[3]);   // R:161: three true divisions, no reciprocal
     float ny = __fdiv_rn(v[1], v[3]);
-    float nz = __fdiv_rn(v[2], v[3]);
+    float nz = WITH_Z ? __fdiv_rn(v[2], v[3]) : 0.0f;
     float ux = __fadd_rn(__fmul_rn(nx, 0.5f), 0.5f);    // R:166
     float uy = __fadd_rn(__fmul_rn(ny, -0.5f), 0.5f);
     return make_float3(__fmul_rn(ux, fw), __fmul_rn(uy, fh), nz);   // R:168 (no rounding of the product)

@@ -18,7 +18,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsr_cuda.so")
+LIB_PATH = os.environ.get("SR_LIB") or os.path.join(_HERE, "libsr_cuda.so")   # SR_LIB: a debug build (e.g. -DSR_TIMELINE)
 
 SR_OK, SR_ERR_ARG, SR_ERR_INDEX, SR_ERR_DOMAIN, SR_ERR_CUDA, SR_ERR_NOMESH = 0, -1, -2, -3, -4, -5
 FLAG_DEPTH_LESS = 1 << 0
