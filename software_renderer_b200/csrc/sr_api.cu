@@ -94,7 +94,7 @@ struct sr_ctx {
     // staging for the host-pointer API (double buffered)
     DevBuf<uint8_t> out_color[2];
     DevBuf<float> out_depth[2];
-    cudaEvent_t ev_render[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
+    cudaEvent_t ev_render[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr}, ev_clear[2] = {nullptr, nullptr};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
 
     // profiling
@@ -527,7 +527,8 @@ int sr_create(sr_ctx** out, int device) {
               cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < 2; ++i)
         ok = cudaEventCreateWithFlags(&c->ev_render[i], cudaEventDisableTiming) == cudaSuccess &&
-             cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming) == cudaSuccess;
+             cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->ev_clear[i], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreate(&c->ev_begin) == cudaSuccess && cudaEventCreate(&c->ev_end) == cudaSuccess;
     for (int i = 0; ok && i <= MAX_PROF; ++i) ok = cudaEventCreate(&c->prof_ev[i]) == cudaSuccess;
     if (!ok) { sr_destroy(c); return SR_ERR_CUDA; }
@@ -547,6 +548,7 @@ void sr_destroy(sr_ctx* c) {
         c->out_color[i].release(); c->out_depth[i].release();
         if (c->ev_render[i]) cudaEventDestroy(c->ev_render[i]);
         if (c->ev_copy[i]) cudaEventDestroy(c->ev_copy[i]);
+        if (c->ev_clear[i]) cudaEventDestroy(c->ev_clear[i]);
     }
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -670,6 +672,11 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
     c->launches = 0;
     cudaStream_t st = c->stream;
     const bool want_depth = !(flags & SR_FLAG_NO_DEPTH_OUT);
+    // Depth test off (or a primitive type that never tests depth): the pass only clears the depth image (R:206) and
+    // never writes it again.  The clear then runs as its own kernel at the start of the frame and the cleared image
+    // crosses PCIe while the frame renders; the tile kernel is told not to write depth.
+    const bool early_depth = want_depth && !((flags & SR_FLAG_DEPTH_LESS) && prim == SR_TRIANGLE);
+    const uint32_t view_flags = early_depth ? (flags | SR_FLAG_NO_DEPTH_OUT) : flags;
     const size_t npx = (size_t)W * H;
     rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
     if (rc) return rc;
@@ -683,12 +690,20 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
     for (size_t i = 0; i < nviews; ++i) {
         const int b = (int)(i & 1);
         if (i >= 2) SR_CUDA(c, cudaStreamWaitEvent(st, c->ev_copy[b], 0));
-        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[b].p, want_depth ? c->out_depth[b].p : nullptr, flags, st, c->status.p + i);
+        if (early_depth) {      // the render stream clears (it runs ahead of the copies), the copy stream only copies
+            k_clear_depth<<<div_up(div_up(npx, 4), 256), 256, 0, st>>>(c->out_depth[b].p, npx);
+            SR_CUDA(c, cudaGetLastError());
+            c->launches++;
+            SR_CUDA(c, cudaEventRecord(c->ev_clear[b], st));
+            SR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_clear[b], 0));
+            SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[b].p, npx * sizeof(float), cudaMemcpyDeviceToHost, c->copy_stream));
+        }
+        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[b].p, (want_depth && !early_depth) ? c->out_depth[b].p : nullptr, view_flags, st, c->status.p + i);
         if (rc) return rc;
         SR_CUDA(c, cudaEventRecord(c->ev_render[b], st));
         SR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_render[b], 0));
         SR_CUDA(c, cudaMemcpyAsync(color + 4 * npx * i, c->out_color[b].p, 4 * npx, cudaMemcpyDeviceToHost, c->copy_stream));
-        if (want_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[b].p, npx * sizeof(float), cudaMemcpyDeviceToHost, c->copy_stream));
+        if (want_depth && !early_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[b].p, npx * sizeof(float), cudaMemcpyDeviceToHost, c->copy_stream));
         SR_CUDA(c, cudaEventRecord(c->ev_copy[b], c->copy_stream));
     }
     SR_CUDA(c, cudaEventRecord(c->ev_end, st));
@@ -701,10 +716,10 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
         if (rerun.empty()) break;
         for (size_t i : rerun) {
             SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
-            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[0].p, want_depth ? c->out_depth[0].p : nullptr, flags, st, c->status.p + i);
+            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[0].p, (want_depth && !early_depth) ? c->out_depth[0].p : nullptr, view_flags, st, c->status.p + i);
             if (rc) return rc;
             SR_CUDA(c, cudaMemcpyAsync(color + 4 * npx * i, c->out_color[0].p, 4 * npx, cudaMemcpyDeviceToHost, st));
-            if (want_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[0].p, npx * sizeof(float), cudaMemcpyDeviceToHost, st));
+            if (want_depth && !early_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[0].p, npx * sizeof(float), cudaMemcpyDeviceToHost, st));
         }
     }
 #ifdef SR_TIMELINE

@@ -1104,6 +1104,15 @@ __global__ void __launch_bounds__(128) k2d_triangle(unsigned* __restrict__ img, 
     }
 }
 
+// The depth clear of R:206 as its own kernel (host API, depth test off: the pass never writes depth again, so the
+// cleared image can travel to the host while the frame renders).
+__global__ void __launch_bounds__(256) k_clear_depth(float* __restrict__ p, size_t n) {
+    const float inf = __int_as_float(0x7f800000);
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i + 4 <= n) *reinterpret_cast<float4*>(p + i) = make_float4(inf, inf, inf, inf);
+    else for (size_t k = i; k < n; ++k) p[k] = inf;
+}
+
 __global__ void k_fill_u64(unsigned long long* __restrict__ p, size_t n, unsigned long long value) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = value;
