@@ -236,7 +236,8 @@ def run_cuda(args):
             dist.barrier()
         t_wall = time.perf_counter() - t_wall0
         clocks = sampler.stop()
-    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    per_frame = np.array([a.elapsed_time(b) for a, b in evs])         # this rank's frames, ms each
+    dev_ms = float(per_frame.sum())
     dev_ms = max_over_ranks(dev_ms, device=dev)
     value = world * K / (dev_ms / 1000.0)
 
@@ -323,6 +324,8 @@ def run_cuda(args):
                        "depth_test": bool(args.depth_test), "l2": "flushed between timed frames (256 MiB fill)",
                        "parallelism": f"{world} independent view streams, one per GPU"},
             "gtri_per_s": value * ntris / 1e9,
+            "frame_ms_rank0": {"median": float(np.median(per_frame)), "p10": float(np.percentile(per_frame, 10)),
+                               "p90": float(np.percentile(per_frame, 90))},
             "frame_roofline": {"bound": "hbm", "achieved": frame_bytes / (frame_ms * 1e-3) / 1e9, "peak": hbm,
                                "unit": "GB/s", "frac": frame_bytes / (frame_ms * 1e-3) / 1e9 / hbm,
                                "bytes_per_frame": frame_bytes, "peak_kind": peak_kind},
@@ -353,8 +356,8 @@ def run_cuda(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--workload", default="soup1m", choices=sorted(WORKLOADS))
     ap.add_argument("--depth-test", type=int, default=0)
