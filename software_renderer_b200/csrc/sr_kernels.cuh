@@ -31,6 +31,9 @@ constexpr int SMALL_MAX = 8;         // direct path: clipped bbox at most SMALL_
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;        // per thread -> 2048 counters per CTA
 constexpr int TILE_BATCH = 16;
+#ifndef SR_SETUP_MINB
+#define SR_SETUP_MINB 5
+#endif       // resident CTAs per SM asked of the binning k_setup variants
 #ifndef SR_TILE_MINB
 #define SR_TILE_MINB 5
 #endif       // triangles per coverage batch in k_tile
@@ -223,7 +226,7 @@ struct XformIn {
     float fw, fh;
 };
 template <bool DEPTH, bool BIN, bool XFORM>
-__global__ void __launch_bounds__(256, (BIN || DEPTH) ? 1 : 8) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
+__global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
