@@ -118,6 +118,15 @@ int sr_render_device(sr_ctx* ctx, const float* transforms_colmajor16, size_t nvi
                      int width, int height, void* color_bgra_dev, void* depth_dev, uint32_t flags,
                      void* cuda_stream);
 
+/* Screen-band split of ONE frame (tiles are independent, so a frame splits by rows).
+ * After sr_set_band(ctx, y0, y1) every render call above produces only rows [y0, y1) of the `height`-row frame it
+ * names: the colour / depth images it writes hold (y1 - y0) rows of `width` pixels (per view), bit-identical to
+ * those rows of the whole frame (R:204-230 keeps no state across rows; the span rule R:467-494 depends on row
+ * differences only, shading R:251-268 is evaluated in frame coordinates).  Ranks of a multi-GPU job render
+ * disjoint bands of the same frame and gather them (multi_gpu.gather_bands).  (0, 0) returns to whole frames.
+ * A band that ends below the image makes the render call fail with SR_ERR_ARG. */
+int sr_set_band(sr_ctx* ctx, int y0, int y1);
+
 /* Waits for the work enqueued by sr_render_device and returns its status (SR_OK / SR_ERR_DOMAIN / SR_ERR_CUDA). */
 int sr_sync(sr_ctx* ctx);
 

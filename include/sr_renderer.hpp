@@ -66,13 +66,18 @@ public:
         mesh_v_ = v.data(); mesh_i_ = i.data(); mesh_nv_ = v.size(); mesh_ni_ = i.size();
     }
 
+    // Screen-band split of one frame: later render() calls write only rows [y0, y1) of the pass's images (bit-identical
+    // to those rows of the whole frame); setBand(0, 0) returns to whole frames.
+    void setBand(int y0, int y1) { check(sr_set_band(ctx_, y0, y1)); band_y0_ = y1 > 0 ? y0 : 0; }
+
     // render(renderPass:) — synchronous; writes colorBuffer and depthBuffer in place.  Returns the number of
     // primitives skipped by the domain rule (0 for every input the reference itself can render).
     uint64_t render(const RenderPass& rp) {
         if (rp.vertices.data() != mesh_v_ || rp.indices.data() != mesh_i_ || rp.vertices.size() != mesh_nv_ || rp.indices.size() != mesh_ni_)
             setMesh(rp.vertices, rp.indices);
+        const size_t skip = static_cast<size_t>(band_y0_) * rp.colorBuffer.width;   // packed rows: a band is one block
         int rc = sr_render(ctx_, &rp.transform.columns[0][0], static_cast<int>(rp.primitiveType), rp.colorBuffer.width,
-                           rp.colorBuffer.height, reinterpret_cast<uint8_t*>(rp.colorBuffer.pointer), rp.depthBuffer.pointer,
+                           rp.colorBuffer.height, reinterpret_cast<uint8_t*>(rp.colorBuffer.pointer + skip), rp.depthBuffer.pointer + skip,
                            depthTest ? SR_FLAG_DEPTH_LESS : 0u);
         sr_stats st{};
         sr_get_stats(ctx_, &st);
@@ -105,6 +110,7 @@ private:
     const void* mesh_v_ = nullptr;
     const void* mesh_i_ = nullptr;
     size_t mesh_nv_ = 0, mesh_ni_ = 0;
+    int band_y0_ = 0;
 };
 
 }  // namespace sr

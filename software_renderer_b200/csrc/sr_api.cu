@@ -109,10 +109,13 @@ struct sr_ctx {
     struct Pending {
         bool active = false;
         std::vector<ViewJob> jobs;
-        int prim = 0, width = 0, height = 0;
+        int prim = 0, width = 0, height = 0, frame_height = 0, y_org = 0;   // height = rows rendered (the band's)
         uint32_t flags = 0;
         cudaStream_t stream = nullptr;
     } pending;
+
+    // sr_set_band: render calls produce rows [band_y0, band_y1) of the frame only (band_y1 == 0: the whole frame)
+    int band_y0 = 0, band_y1 = 0;
 
     sr_stats stats = {};
     uint64_t launches = 0;
@@ -242,8 +245,13 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
     return SR_OK;
 }
 
-// Enqueue one render pass (R:204-230) on `st`.  Outputs are device pointers.
-int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint8_t* color_dev, float* depth_dev,
+// Rows of the frame a call renders: the band set by sr_set_band, else all H.
+struct Band { int y0, rows; };
+inline Band band_of(const sr_ctx* c, int H) { return c->band_y1 > 0 ? Band{c->band_y0, c->band_y1 - c->band_y0} : Band{0, H}; }
+
+// Enqueue one render pass (R:204-230) on `st`.  Outputs are device pointers to images of `H` rows: rows
+// [y_org, y_org + H) of the frame, whose full height `Hframe` only enters the viewport mapping (R:165-172).
+int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int Hframe, int y_org, uint8_t* color_dev, float* depth_dev,
                  uint32_t flags, cudaStream_t st, ViewStatus* d_status) {
     const bool depth_mode = (flags & SR_FLAG_DEPTH_LESS) != 0 && prim == SR_TRIANGLE;
     if (flags & SR_FLAG_NO_DEPTH_OUT) depth_dev = nullptr;
@@ -258,13 +266,13 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
     const bool batched_frame = prim == SR_TRIANGLE && !depth_mode && c->batched_mode && (c->nidx / 3) >= (1u << 16);
     if (prim != SR_LINE && nverts > 0 && !batched_frame) {
         prof_mark(c, st, "k_transform");
-        launch_pdl(c, k_transform, div_up(nverts, 256), 256, st, c->pos.p, nverts, M, (float)W, (float)H, c->sv.p);
+        launch_pdl(c, k_transform, div_up(nverts, 256), 256, st, c->pos.p, nverts, M, (float)W, (float)Hframe, c->sv.p);
         c->launches++;
     }
     if (prim == SR_TRIANGLE) {
         const int ntris = (int)(c->nidx / 3);
         FrameParams fp;
-        fp.width = W; fp.height = H;
+        fp.width = W; fp.height = H; fp.y_org = y_org;
         fp.tiles_x = (int)div_up(W, TILE); fp.tiles_y = (int)div_up(H, TILE);
         fp.ntiles = fp.tiles_x * fp.tiles_y;
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
@@ -301,7 +309,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 auto ks = depth_mode ? (fp.nobin ? k_setup<true, false, false> : k_setup<true, true, false>)
                                      : (fp.nobin ? k_setup<false, false, false>
                                                  : (fp.batched ? k_setup<false, true, true> : k_setup<false, true, false>));
-                XformIn xf{c->pos.p, M, (float)W, (float)H};
+                XformIn xf{c->pos.p, M, (float)W, (float)Hframe};
                 launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
             }
@@ -323,7 +331,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
                 prof_mark(c, st, "k_resolve");
                 const bool wide = npx >= (4u << 20);       // four pixels per thread once that still fills the GPU
                 auto kr = depth_mode ? (wide ? k_resolve<true, 4> : k_resolve<true, 1>) : (wide ? k_resolve<false, 4> : k_resolve<false, 1>);
-                launch_pdl(c, kr, div_up(div_up(npx, wide ? 4 : 1), 256), 256, st, in, W, npx, c->vis32.p, c->vis64.p, color32, depth_dev);
+                launch_pdl(c, kr, div_up(div_up(npx, wide ? 4 : 1), 256), 256, st, in, W, y_org, npx, c->vis32.p, c->vis64.p, color32, depth_dev);
                 c->launches++;
                 continue;
             }
@@ -340,7 +348,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, uint
             const int ncorners = (int)((c->nidx / 3) * 3);
             if (ncorners > 0) {
                 prof_mark(c, st, "k_points_scatter");
-                launch_pdl(c, k_points_scatter, div_up(ncorners, 256), 256, st, c->idx.p, c->sv.p, ncorners, W, H, c->vis32.p, d_status);
+                launch_pdl(c, k_points_scatter, div_up(ncorners, 256), 256, st, c->idx.p, c->sv.p, ncorners, W, H, y_org, c->vis32.p, d_status);
                 c->launches++;
             }
         }
@@ -359,6 +367,7 @@ int check_args(sr_ctx* c, const float* transforms, size_t nviews, int prim, int 
     if (!transforms || !color || nviews == 0) return fail(c, SR_ERR_ARG, "null transform/colour pointer or zero views");
     if (!depth && !(flags & SR_FLAG_NO_DEPTH_OUT)) return fail(c, SR_ERR_ARG, "depth pointer is null without SR_FLAG_NO_DEPTH_OUT");
     if (W <= 0 || H <= 0 || (size_t)W * H > (1u << 30)) return fail(c, SR_ERR_ARG, "bad image size");
+    if (c->band_y1 > H) return fail(c, SR_ERR_ARG, "the band set by sr_set_band ends below the image");
     if (prim < SR_TRIANGLE || prim > SR_VERTICES) return fail(c, SR_ERR_ARG, "unknown primitive type");
     if (!c->has_mesh) return fail(c, SR_ERR_NOMESH, "sr_set_mesh has not been called");
     const size_t per = primitive_vertices(prim);
@@ -474,7 +483,7 @@ int finish_pending(sr_ctx* c) {
         if (rerun.empty()) break;
         for (size_t i : rerun) {
             SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
-            rc = enqueue_view(c, p.jobs[i].m, p.prim, p.width, p.height, p.jobs[i].color, p.jobs[i].depth, p.flags, st, c->status.p + i);
+            rc = enqueue_view(c, p.jobs[i].m, p.prim, p.width, p.height, p.frame_height, p.y_org, p.jobs[i].color, p.jobs[i].depth, p.flags, st, c->status.p + i);
             if (rc) return rc;
         }
     }
@@ -615,10 +624,13 @@ int sr_render_device(sr_ctx* c, const float* transforms, size_t nviews, int prim
     if (rc) return rc;
     SR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    const int Hframe = H;
+    const Band band = band_of(c, H);
+    H = band.rows;                                             // images hold the band's rows
     auto& p = c->pending;
     // calls with the same target format on the same stream accumulate (no host round trip between them)
     const size_t kStatusViews = 1024;
-    if (p.active && (p.prim != prim || p.width != W || p.height != H || p.flags != flags || p.stream != st ||
+    if (p.active && (p.prim != prim || p.width != W || p.height != H || p.frame_height != Hframe || p.y_org != band.y0 || p.flags != flags || p.stream != st ||
                      p.jobs.size() + nviews > std::max(c->status.cap, kStatusViews))) {
         rc = sr_sync(c);
         if (rc == SR_ERR_CUDA) return rc;
@@ -640,14 +652,14 @@ int sr_render_device(sr_ctx* c, const float* transforms, size_t nviews, int prim
         SR_CUDA(c, cudaEventRecord(c->ev_begin, st));
     }
     p.active = true;
-    p.prim = prim; p.width = W; p.height = H; p.flags = flags; p.stream = st;
+    p.prim = prim; p.width = W; p.height = H; p.frame_height = Hframe; p.y_org = band.y0; p.flags = flags; p.stream = st;
     for (size_t i = 0; i < nviews; ++i) {
         sr_ctx::ViewJob job;
         std::memcpy(job.m, transforms + 16 * i, sizeof job.m);
         job.color = color + 4 * npx * i;
         job.depth = depth ? depth + npx * i : nullptr;
         p.jobs.push_back(job);
-        rc = enqueue_view(c, job.m, prim, W, H, job.color, job.depth, flags, st, c->status.p + first + i);
+        rc = enqueue_view(c, job.m, prim, W, H, Hframe, band.y0, job.color, job.depth, flags, st, c->status.p + first + i);
         if (rc) return rc;
     }
     SR_CUDA(c, cudaEventRecord(c->ev_end, st));
@@ -671,6 +683,9 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
     c->stats = sr_stats{};
     c->launches = 0;
     cudaStream_t st = c->stream;
+    const int Hframe = H;
+    const Band band = band_of(c, H);
+    H = band.rows;                                             // images hold the band's rows
     const bool want_depth = !(flags & SR_FLAG_NO_DEPTH_OUT);
     // Depth test off (or a primitive type that never tests depth): the pass only clears the depth image (R:206) and
     // never writes it again.  The clear then runs as its own kernel at the start of the frame and the cleared image
@@ -698,7 +713,7 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
             SR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_clear[b], 0));
             SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[b].p, npx * sizeof(float), cudaMemcpyDeviceToHost, c->copy_stream));
         }
-        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[b].p, (want_depth && !early_depth) ? c->out_depth[b].p : nullptr, view_flags, st, c->status.p + i);
+        rc = enqueue_view(c, transforms + 16 * i, prim, W, H, Hframe, band.y0, c->out_color[b].p, (want_depth && !early_depth) ? c->out_depth[b].p : nullptr, view_flags, st, c->status.p + i);
         if (rc) return rc;
         SR_CUDA(c, cudaEventRecord(c->ev_render[b], st));
         SR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_render[b], 0));
@@ -716,7 +731,7 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
         if (rerun.empty()) break;
         for (size_t i : rerun) {
             SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
-            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, c->out_color[0].p, (want_depth && !early_depth) ? c->out_depth[0].p : nullptr, view_flags, st, c->status.p + i);
+            rc = enqueue_view(c, transforms + 16 * i, prim, W, H, Hframe, band.y0, c->out_color[0].p, (want_depth && !early_depth) ? c->out_depth[0].p : nullptr, view_flags, st, c->status.p + i);
             if (rc) return rc;
             SR_CUDA(c, cudaMemcpyAsync(color + 4 * npx * i, c->out_color[0].p, 4 * npx, cudaMemcpyDeviceToHost, st));
             if (want_depth && !early_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[0].p, npx * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -814,6 +829,15 @@ int sr_draw2d(sr_ctx* c, const sr_cmd2d* cmds, size_t n, int W, int H, uint8_t* 
     c->stats = sr_stats{};
     c->stats.primitives = n;
     c->stats.gpu_launches = c->launches;
+    return SR_OK;
+}
+
+int sr_set_band(sr_ctx* c, int y0, int y1) {
+    if (!c) return SR_ERR_ARG;
+    if (!(y0 == 0 && y1 == 0) && !(0 <= y0 && y0 < y1)) return fail(c, SR_ERR_ARG, "sr_set_band: need 0 <= y0 < y1, or (0, 0) for the whole frame");
+    if (c->pending.active) { int rc = sr_sync(c); if (rc == SR_ERR_CUDA) return rc; }   // enqueued views keep the band they were given
+    c->band_y0 = y0;
+    c->band_y1 = y1;
     return SR_OK;
 }
 

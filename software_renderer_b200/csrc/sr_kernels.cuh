@@ -142,7 +142,11 @@ __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ pos
 // later batches neither bin nor rasterize into it.  The image is identical to the sequential loop's.
 // ---------------------------------------------------------------------------------------------------------------
 struct FrameParams {
-    int width, height;
+    int width, height;        // the image the kernels work on: the whole frame, or a band of its rows (sr_set_band)
+    int y_org;                // first frame row of that image (0 for a whole frame).  Integer corners are moved to
+                              //   band-local rows right after the truncation of R:271: the span rule (R:467-494) only
+                              //   uses differences of y, so coverage is unchanged; everything that feeds FLOAT math
+                              //   (ws / depth, R:251-257) keeps frame coordinates (local row + y_org)
     int tiles_x, tiles_y, ntiles;
     unsigned pair_capacity;
     unsigned epoch;           // frame stamp for tile_done[]
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
             ax = __float2int_rz(a.x); ay = __float2int_rz(a.y);     // simd_long2(...) truncates toward zero
             bx = __float2int_rz(b.x); by = __float2int_rz(b.y);
             cx = __float2int_rz(c.x); cy = __float2int_rz(c.y);
-            s = sort_corners(ax, ay, bx, by, cx, cy, perm);
+            s = sort_corners(ax, ay - fp.y_org, bx, by - fp.y_org, cx, cy - fp.y_org, perm);   // band-local rows (|y| < 2^30, no overflow)
             // result-preserving clip/cull: off-screen pixels are rejected one by one by R:246-250
             y0 = max(s.y0, 0);
             y1 = min(s.y2, fp.height - 1);
@@ -305,7 +309,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
                     if (late && tile_retired(fp, x >> TILE_SHIFT, y >> TILE_SHIFT)) return;
                     const size_t o = (size_t)y * fp.width + x;
                     if (DEPTH) {
-                        const float d = blend3(a.z, b.z, c.z, bary_weights(bt, x, y));
+                        const float d = blend3(a.z, b.z, c.z, bary_weights(bt, x, y + fp.y_org));
                         if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, (unsigned)prim));
                     } else {
                         atomicMax(vis32 + o, (unsigned)prim + 1u);
@@ -387,10 +391,10 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
             float dlo = __int_as_float(0x7fc00000), zmin = 0.0f, zmax = 0.0f;
             if (large) {
                 const BaryT bt = bary_setup(ax, ay, bx, by, cx, cy);
-                DepthSample m = depth_sample(bt, za, zb, zc, xmin, y0);
+                DepthSample m = depth_sample(bt, za, zb, zc, xmin, y0 + fp.y_org);
 #pragma unroll
                 for (int q = 1; q < 4; ++q) {
-                    const DepthSample t = depth_sample(bt, za, zb, zc, (q & 1) ? xmax : xmin, (q & 2) ? y1 : y0);
+                    const DepthSample t = depth_sample(bt, za, zb, zc, (q & 1) ? xmax : xmin, ((q & 2) ? y1 : y0) + fp.y_org);
                     m.d = fminf(m.d, t.d); m.a = fmaxf(m.a, t.a); m.b = fmaxf(m.b, t.b);
                 }
                 // the better of two rigorous bounds: over the clipped bbox rectangle, over the covered pixels
@@ -464,7 +468,7 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
                 if (late && tile_retired(fp, x >> TILE_SHIFT, y >> TILE_SHIFT)) continue;
                 const size_t o = (size_t)y * fp.width + x;
                 if (DEPTH) {
-                    const float3 w = bary_weights(s_bt[wbase + src], x, y);
+                    const float3 w = bary_weights(s_bt[wbase + src], x, y + fp.y_org);
                     const float d = blend3(s_z[wbase + src][0], s_z[wbase + src][1], s_z[wbase + src][2], w);
                     if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, t.prim));
                 } else {
@@ -820,7 +824,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             const TriRec& t = s_rec[cur][j];
             int oc[6];
             unsort_corners(t, oc);
-            s_bt[j] = bary_setup(oc[0], oc[1], oc[2], oc[3], oc[4], oc[5]);
+            s_bt[j] = bary_setup(oc[0], oc[1] + fp.y_org, oc[2], oc[3] + fp.y_org, oc[4], oc[5] + fp.y_org);   // frame rows (R:251)
             const float4 z = in.ztri[t.prim];
             s_z[j][0] = z.x; s_z[j][1] = z.y; s_z[j][2] = z.z;
         }
@@ -831,7 +835,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             // is beyond the farthest pixel: each lane samples one corner pixel of the tile, xor-shuffles reduce
             const int jq = j < n ? j : 0;
             DepthSample m = depth_sample(s_bt[jq], s_z[jq][0], s_z[jq][1], s_z[jq][2],
-                                         (row & 1) ? x_hi : x_lo, (row & 2) ? min(ty * TILE + TILE - 1, fp.height - 1) : ty * TILE);
+                                         (row & 1) ? x_hi : x_lo, ((row & 2) ? min(ty * TILE + TILE - 1, fp.height - 1) : ty * TILE) + fp.y_org);
 #pragma unroll
             for (int d = 1; d <= 2; d <<= 1) {
                 m.d = fminf(m.d, __shfl_xor_sync(0xffffffffu, m.d, d));
@@ -876,7 +880,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                 bits &= bits - 1;
                 const int jj = ((b & 15) << 1) | (b >> 4);
                 if (DEPTH) {
-                    const float3 w = bary_weights(s_bt[jj], x, y);
+                    const float3 w = bary_weights(s_bt[jj], x, y + fp.y_org);
                     const float d = blend3(s_z[jj][0], s_z[jj][1], s_z[jj][2], w);
                     if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[jj]));
                 } else {
@@ -924,8 +928,8 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     else       { if (v_in) vis32[o] = 0u; }
     unsigned bgra = 0u;                                  // clear colour (R:205)
     float depth = __int_as_float(0x7f800000);            // +inf (R:206)
-    if (DEPTH) { if (k != SR_KEY_EMPTY) shade_pixel(in, (unsigned)k, x, y, true, bgra, depth); }
-    else       { if (v) shade_pixel(in, v - 1u, x, y, false, bgra, depth); }
+    if (DEPTH) { if (k != SR_KEY_EMPTY) shade_pixel(in, (unsigned)k, x, y + fp.y_org, true, bgra, depth); }
+    else       { if (v) shade_pixel(in, v - 1u, x, y + fp.y_org, false, bgra, depth); }
     color_out[o] = bgra;
     if (depth_out) depth_out[o] = depth;
     }   // tile loop
@@ -938,7 +942,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
 // (R:251-268), 16-B stores of colour and depth (clear fused, R:205-206), words re-armed for the next frame.
 // ---------------------------------------------------------------------------------------------------------------
 template <bool DEPTH, int PPT>                              // PPT pixels per thread: 4 (large images) or 1 (enough threads)
-__global__ void __launch_bounds__(256) k_resolve(ShadeIn in, int W, size_t npx, unsigned* __restrict__ vis32,
+__global__ void __launch_bounds__(256) k_resolve(ShadeIn in, int W, int y_org, size_t npx, unsigned* __restrict__ vis32,
                                                  unsigned long long* __restrict__ vis64, unsigned* __restrict__ color_out,
                                                  float* __restrict__ depth_out) {
     pdl_wait();
@@ -970,6 +974,7 @@ __global__ void __launch_bounds__(256) k_resolve(ShadeIn in, int W, size_t npx, 
         }
     }
     int y = (int)(o / (size_t)W), x = (int)(o - (size_t)y * W);
+    y += y_org;                                             // shading works in frame rows
     unsigned bgra[4];
     float depth[4];
 #pragma unroll
@@ -992,7 +997,7 @@ __global__ void __launch_bounds__(256) k_resolve(ShadeIn in, int W, size_t npx, 
 // k_points_resolve also serves PrimitiveType.line, which draws nothing (R:289-293): clear only.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_points_scatter(const int* __restrict__ idx, const float4* __restrict__ sv, int ncorners,
-                                                        int W, int H, unsigned* __restrict__ vis32, ViewStatus* __restrict__ status) {
+                                                        int W, int H, int y_org, unsigned* __restrict__ vis32, ViewStatus* __restrict__ status) {
     pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     bool skipped = false;
@@ -1001,7 +1006,7 @@ __global__ void __launch_bounds__(256) k_points_scatter(const int* __restrict__ 
         if (!(in_domain(s.x) && in_domain(s.y))) {
             skipped = true;
         } else {
-            const int x = __float2int_rz(s.x), y = __float2int_rz(s.y);     // Int(v.xyz.x) R:298-299
+            const int x = __float2int_rz(s.x), y = __float2int_rz(s.y) - y_org;     // Int(v.xyz.x) R:298-299; band-local row
             if (x >= 0 && x < W && y >= 0 && y < H) atomicMax(vis32 + (size_t)y * W + x, (unsigned)c + 1u);  // R:30-36
         }
     }

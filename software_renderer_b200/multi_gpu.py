@@ -3,7 +3,8 @@ rendering.  A collective is used only when a composite is requested: finished fr
 (NCCL over NVLink on the GPU box; the same code runs on gloo/CPU tensors for the host-logic tests).
 
 A view depends only on (mesh, matrix, width, height) — Renderer.swift:204-230 keeps no cross-frame state — so the
-partition is a plain block split of the view list.
+partition is a plain block split of the view list.  One frame can also be split by rows (`band_range`, `gather_bands`
+over `CudaRenderer.set_band` / `sr_set_band`): tiles are independent, each rank renders a band of tile rows.
 """
 from __future__ import annotations
 
@@ -40,6 +41,42 @@ def gather_framebuffers(local: torch.Tensor, nviews: int, dst: int = 0, group=No
         recv = [torch.empty_like(send) for _ in range(world)]
         dist.gather(send, gather_list=recv, dst=dst, group=group)
         return torch.cat([recv[r][: sizes[r]] for r in range(world)], dim=0)
+    dist.gather(send, gather_list=None, dst=dst, group=group)
+    return None
+
+
+def band_range(height: int, rank: int, world: int, align: int = 16) -> Tuple[int, int]:
+    """Rows [y0, y1) of ONE frame rendered by `rank` (screen-band split): the frame's tile
+    rows (16 pixel rows each, the kernels' tile height) are block-split like views, so every band but the last is
+    a whole number of tiles.  A rank may get an empty band (y0 == y1) when there are fewer tile rows than ranks."""
+    if height <= 0 or align <= 0:
+        raise ValueError("bad height/align")
+    t0, t1 = shard_range((height + align - 1) // align, rank, world)
+    return min(t0 * align, height), min(t1 * align, height)
+
+
+def gather_bands(local: torch.Tensor, height: int, dst: int = 0, group=None, align: int = 16):
+    """Stitches the ranks' bands of one frame (or of n frames): `local` is (n, rows_r, W, C) or (rows_r, W, ...) with
+    rows_r = this rank's band_range; returns the full (n, height, W, C) / (height, W, ...) image on `dst`, None
+    elsewhere.  Bands differ in row count, so each is padded to the tallest for the collective and trimmed."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    spans = [band_range(height, r, world, align) for r in range(world)]
+    rows = [b - a for a, b in spans]
+    batched = local.dim() == 4
+    x = local if batched else local.unsqueeze(0)
+    assert x.shape[1] == rows[rank], "local band does not match band_range"
+    tallest = max(rows)
+    send = x
+    if rows[rank] < tallest:
+        pad = torch.zeros((x.shape[0], tallest - rows[rank]) + tuple(x.shape[2:]), dtype=x.dtype, device=x.device)
+        send = torch.cat([x, pad], dim=1)
+    send = send.contiguous()
+    if rank == dst:
+        recv = [torch.empty_like(send) for _ in range(world)]
+        dist.gather(send, gather_list=recv, dst=dst, group=group)
+        full = torch.cat([recv[r][:, : rows[r]] for r in range(world)], dim=1)
+        return full if batched else full[0]
     dist.gather(send, gather_list=None, dst=dst, group=group)
     return None
 

@@ -28,7 +28,7 @@ FLAG_NO_DEPTH_OUT = 1 << 1
 ABI_SYMBOLS = (
     "sr_version", "sr_create", "sr_destroy", "sr_last_error", "sr_set_mesh", "sr_render", "sr_render_pass",
     "sr_render_batch", "sr_render_device", "sr_sync", "sr_get_stats", "sr_get_kernel_times", "sr_set_profiling",
-    "sr_draw2d",
+    "sr_draw2d", "sr_set_band",
 )
 
 
@@ -148,6 +148,8 @@ def load_library():
     L.sr_set_profiling.argtypes = [vp, i32]
     L.sr_draw2d.restype = i32
     L.sr_draw2d.argtypes = [vp, vp, sz, i32, i32, vp]
+    L.sr_set_band.restype = i32
+    L.sr_set_band.argtypes = [vp, i32, i32]
     _lib = L
     return L
 
@@ -200,6 +202,7 @@ class CudaRenderer:
         self.device = device
         self.depth_test = False      # True = run the depth test of Renderer.swift:257-261
         self._mesh_key = None
+        self._band = None            # (y0, y1): render only these rows of each frame (set_band)
 
     # -- lifetime ----------------------------------------------------------------------------------------------
     def close(self):
@@ -240,9 +243,20 @@ class CudaRenderer:
         self._check(self._lib.sr_set_mesh(self._ctx, v.ctypes.data, v.shape[0], idx.ctypes.data, idx.shape[0]))
         self._mesh_key = None
 
+    # -- screen-band split of one frame ------------------------------------------------------------------------
+    def set_band(self, y0: int = 0, y1: int = 0):
+        """Subsequent render calls produce only rows [y0, y1) of each frame, bit-identical to those rows of the whole
+        frame; output images hold y1 - y0 rows.  set_band() returns to whole frames."""
+        self._check(self._lib.sr_set_band(self._ctx, int(y0), int(y1)))
+        self._band = (int(y0), int(y1)) if y1 > 0 else None
+
+    def _rows(self, height: int) -> int:
+        return height if self._band is None else self._band[1] - self._band[0]
+
     # -- render(renderPass:) -----------------------------------------------------------------------------------
     def render(self, render_pass: RenderPass):
-        """Renderer.render(renderPass:) (Renderer.swift:204-230): synchronous, writes both images in place.
+        """Renderer.render(renderPass:) (Renderer.swift:204-230): synchronous, writes both images in place
+        (with a band set: rows [y0, y1) of both images, the rest is left untouched).
         The mesh arrays travel with the pass, as in the reference (App.swift:163); they are re-uploaded only when
         the array OBJECTS handed over are not the ones uploaded last; after modifying them in place call set_mesh."""
         rp = render_pass
@@ -255,18 +269,23 @@ class CudaRenderer:
         assert col.dtype == np.uint8 and col.flags.c_contiguous and col.size == W * H * 4
         assert dep.dtype == np.float32 and dep.flags.c_contiguous and dep.size == W * H
         m = _colmajor(rp.transform)
+        # with a band set only rows [y0, y1) of the pass's images are written: packed rows, so the band is one block
+        y0 = 0 if self._band is None else self._band[0]
         self._check(self._lib.sr_render(self._ctx, m.ctypes.data, int(rp.primitive_type), W, H,
-                                        col.ctypes.data, dep.ctypes.data, self._flags(True)))
+                                        col.ctypes.data + 4 * W * y0, dep.ctypes.data + 4 * W * y0, self._flags(True)))
 
     def render_views(self, transforms, width: int, height: int, primitive_type=PrimitiveType.triangle,
                      color_out: np.ndarray | None = None, depth_out: np.ndarray | None = None, want_depth=True):
-        """`n` independent render passes of the uploaded mesh.  Returns (color[n,H,W,4], depth[n,H,W] or None)."""
+        """`n` independent render passes of the uploaded mesh.  Returns (color[n,H,W,4], depth[n,H,W] or None);
+        with a band set (set_band) the images hold the band's rows only."""
         m = _colmajor(np.asarray(transforms, dtype=np.float32).reshape(-1, 4, 4))
         n = m.shape[0]
-        color = color_out if color_out is not None else np.empty((n, height, width, 4), dtype=np.uint8)
+        rows = self._rows(height)
+        color = color_out if color_out is not None else np.empty((n, rows, width, 4), dtype=np.uint8)
         depth = None
         if want_depth:
-            depth = depth_out if depth_out is not None else np.empty((n, height, width), dtype=np.float32)
+            depth = depth_out if depth_out is not None else np.empty((n, rows, width), dtype=np.float32)
+        assert color.size == n * rows * width * 4 and (depth is None or depth.size == n * rows * width)
         rc = self._lib.sr_render_batch(self._ctx, m.ctypes.data, n, int(primitive_type), width, height,
                                        color.ctypes.data, depth.ctypes.data if depth is not None else None,
                                        self._flags(want_depth))

@@ -72,6 +72,15 @@ public final class CudaRenderer {
     }
     deinit { sr_destroy(ctx) }
 
+    /// Screen-band split of one frame: later render(renderPass:) calls write only rows y0 ..< y1 of the pass's images,
+    /// bit-identical to those rows of the whole frame; setBand(0, 0) returns to whole frames.
+    private var bandStart = 0
+    public func setBand(_ y0: Int, _ y1: Int) {
+        let rc = sr_set_band(ctx, Int32(y0), Int32(y1))
+        precondition(rc == 0, String(cString: sr_last_error(ctx)))
+        bandStart = y1 > 0 ? y0 : 0
+    }
+
     /// Same signature and contract as Renderer.render(renderPass:) (Renderer.swift:204): synchronous, writes
     /// colorBuffer and depthBuffer in place.
     public func render(renderPass: RenderPass) {
@@ -92,10 +101,11 @@ public final class CudaRenderer {
         }
         var m = renderPass.transform
         let flags: UInt32 = depthTest ? UInt32(SR_FLAG_DEPTH_LESS) : 0
+        let skip = bandStart * renderPass.colorBuffer.width          // packed rows: a band is one block of the image
         let rc = withUnsafeBytes(of: &m) { mb in
             sr_render(ctx, mb.baseAddress!.assumingMemoryBound(to: Float.self), renderPass.primitiveType.raw, w, h,
-                      UnsafeMutableRawPointer(renderPass.colorBuffer.pointer).assumingMemoryBound(to: UInt8.self),
-                      renderPass.depthBuffer.pointer, flags)
+                      UnsafeMutableRawPointer(renderPass.colorBuffer.pointer + skip).assumingMemoryBound(to: UInt8.self),
+                      renderPass.depthBuffer.pointer + skip, flags)
         }
         var st = sr_stats()
         sr_get_stats(ctx, &st)

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from software_renderer_b200 import scene as S  # noqa: E402
-from software_renderer_b200.multi_gpu import gather_framebuffers, max_over_ranks, shard_range  # noqa: E402
+from software_renderer_b200.multi_gpu import band_range, gather_bands, gather_framebuffers, max_over_ranks, shard_range  # noqa: E402
 
 NVIEWS, W, H = 5, 96, 64
 
@@ -73,3 +73,48 @@ def test_sharded_views_gather_equals_single_process(tmp_path):
     got = np.load(path)
     want = _render_views(S.fibonacci_views(NVIEWS))
     assert got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_band_range_partitions_rows_on_tile_boundaries():
+    for height in (1, 15, 16, 17, 200, 1080, 2160):
+        for world in (1, 2, 3, 4, 8):
+            spans = [band_range(height, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == height
+            for a, b in zip(spans, spans[1:]):
+                assert a[1] == b[0] and a[0] <= a[1]
+            assert all(y0 % 16 == 0 for y0, _ in spans if y0 < height)
+            tiles = [(y1 - y0 + 15) // 16 for y0, y1 in spans]
+            assert max(tiles) - min(tiles) <= 1
+    assert band_range(1080, 7, 8) == (960, 1080)       # 68 tile rows over 8 ranks: 9,9,9,9,8,8,8,8; the last is partial
+    with pytest.raises(ValueError):
+        band_range(0, 0, 1)
+
+
+def _band_worker(rank, world, port, result_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        frames = _render_views(S.fibonacci_views(2))                 # (2, H, W, 4): every rank could render the frame;
+        y0, y1 = band_range(H, rank, world)                          # it keeps only its band, as sr_set_band would
+        full = gather_bands(torch.from_numpy(frames[:, y0:y1].copy()), H, dst=0)
+        one = gather_bands(torch.from_numpy(frames[0, y0:y1].copy()), H, dst=0)
+        if rank == 0:
+            np.save(result_path, np.concatenate([full.numpy(), one.numpy()[None]], axis=0))
+        else:
+            assert full is None and one is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_banded_frame_gather_equals_whole_frame(tmp_path, world):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    path = str(tmp_path / "bands.npy")
+    mp.spawn(_band_worker, args=(world, port, path), nprocs=world, join=True)
+    got = np.load(path)
+    want = _render_views(S.fibonacci_views(2))
+    assert np.array_equal(got[:2], want) and np.array_equal(got[2], want[0])
