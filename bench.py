@@ -2,6 +2,7 @@
 """bench.py — frames/s of the rasterization hot path (BASELINE.json metric) on N B200s of one node.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload soup1m|ico80k|cs10m4k|views512] [--impl reference]
+                  [--depth-test 1] [--split-frame 1]
 
 A "step" is one render pass (Renderer.render(renderPass:), Renderer.swift:204-230) of the named workload with that
 step's own transform.  Default workload: BASELINE.json's metric config — 1M-triangle soup at 1920x1080 (configs[2]).
@@ -353,6 +354,104 @@ def run_cuda(args):
         print(json.dumps(line), flush=True)
 
 
+def run_split(args):
+    """--split-frame 1: ONE frame per step, split by rows over the ranks (sr_set_band).  Each
+    rank renders its band of tile rows of the same frame, the bands are gathered to rank 0 over NCCL inside the timed
+    region (this mode's only collective), so value = whole frames/s as seen by rank 0: strong scaling.  Not the
+    headline mode (independent frames need no exchange at all); it measures single-frame latency across GPUs."""
+    import torch
+    import torch.distributed as dist
+    import software_renderer_b200 as srb
+    from software_renderer_b200.multi_gpu import band_range, gather_bands, max_over_ranks
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    desc, W, H, v, i, xf = make_workload(args.workload)
+    ntris, nverts = i.size // 3, int(v.shape[0])
+    K, Wm = args.steps, args.warmup
+    r = srb.CudaRenderer(local)
+    r.depth_test = bool(args.depth_test)
+    r.set_mesh(v, i)
+    y0, y1 = band_range(H, rank, world)
+    assert y1 > y0, "fewer tile rows than ranks"
+    if world > 1:
+        r.set_band(y0, y1)
+    color = torch.empty((y1 - y0, W, 4), dtype=torch.uint8, device=dev)
+    depth = torch.empty((y1 - y0, W), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    full = None
+
+    def frame(k):
+        r.render_device(xf(k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream, sync=False)
+        if world > 1:
+            return gather_bands(color, H, dst=0), gather_bands(depth, H, dst=0)
+        return color, depth
+
+    with torch.cuda.stream(stream):
+        frame(0)
+        r.sync()
+        for k in range(1, Wm):
+            frame(k)
+        r.sync()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        for k in range(K):
+            flush.fill_(k & 0xFF)
+            evs[k][0].record(stream)
+            full = frame(Wm + k)
+            evs[k][1].record(stream)
+        r.sync()
+        launches = r.stats()["gpu_launches"]
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        clocks = sampler.stop()
+    per_frame = np.array([a.elapsed_time(b) for a, b in evs])
+    dev_ms = max_over_ranks(float(per_frame.sum()), device=dev)
+    value = K / (dev_ms / 1000.0)
+    line = None
+    if rank == 0:
+        # the stitched frame of the last step against this rank's own whole-frame render of the same transform
+        got_c, got_d = full[0].cpu().numpy(), full[1].cpu().numpy()
+        r.set_band()
+        want_c, want_d = r.render_views(xf(Wm + K - 1)[None], W, H)
+        same = bool(np.array_equal(got_c, want_c[0]) and np.array_equal(got_d.view(np.uint32), want_d[0].view(np.uint32)))
+        hbm, peak_kind = peaks()
+        from software_renderer_b200 import scene as S
+        frame_bytes = S.algorithmic_bytes(ntris, nverts, W, H)
+        line = {
+            "metric": "frames_per_second", "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32+i64", "data": "synthetic",
+            "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": nverts,
+                       "depth_test": bool(args.depth_test), "l2": "flushed between timed frames (256 MiB fill)",
+                       "parallelism": f"one frame split into {world} bands of tile rows, NCCL gather of the bands to rank 0 inside the timed region"},
+            "frame_ms_rank0": {"median": float(np.median(per_frame)), "p10": float(np.percentile(per_frame, 10)),
+                               "p90": float(np.percentile(per_frame, 90))},
+            "frame_roofline": {"bound": "hbm", "achieved": frame_bytes / (dev_ms / K * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                               "frac": frame_bytes / (dev_ms / K * 1e-3) / 1e9 / hbm, "bytes_per_frame": frame_bytes, "peak_kind": peak_kind},
+            "bands_equal_whole_frame": same,
+            "gathered_bytes_per_frame": 0 if world == 1 else 8 * W * (H - (y1 - y0)),
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+    r.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -361,10 +460,13 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--workload", default="soup1m", choices=sorted(WORKLOADS))
     ap.add_argument("--depth-test", type=int, default=0)
+    ap.add_argument("--split-frame", type=int, default=0, help="1: every step is ONE frame split by rows over the ranks")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":
         run_reference(args)
+    elif args.split_frame:
+        run_split(args)
     else:
         run_cuda(args)
 
