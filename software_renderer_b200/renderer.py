@@ -285,7 +285,7 @@ class CudaRenderer:
         depth = None
         if want_depth:
             depth = depth_out if depth_out is not None else np.empty((n, rows, width), dtype=np.float32)
-        assert color.size == n * rows * width * 4 and (depth is None or depth.size == n * rows * width)
+        assert color.size >= n * rows * width * 4 and (depth is None or depth.size >= n * rows * width)
         rc = self._lib.sr_render_batch(self._ctx, m.ctypes.data, n, int(primitive_type), width, height,
                                        color.ctypes.data, depth.ctypes.data if depth is not None else None,
                                        self._flags(want_depth))
