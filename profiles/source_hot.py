@@ -29,5 +29,5 @@ for l in lines:
 ti, ts = sum(x[3] for x in src), sum(x[4] for x in src)
 print(f"total warp instructions {ti}, stall samples {ts}")
 print("  file:line   inst%  stall%  source")
-for fn, ln, text, ins, st in sorted(src, key=lambda x: -x[4])[:top]:
+for fn, ln, text, ins, st in sorted(src, key=lambda x: -x[3 if "--by-inst" in sys.argv else 4])[:top]:
     print(f"{fn[:14]:>14}:{ln:<5d} {100 * ins / max(ti, 1):5.1f}  {100 * st / max(ts, 1):5.1f}   {text[:105]}")

@@ -310,7 +310,7 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
                                      : (fp.nobin ? k_setup<false, false, false>
                                                  : (fp.batched ? k_setup<false, true, true> : k_setup<false, true, false>));
                 XformIn xf{c->pos.p, M, (float)W, (float)Hframe};
-                launch_pdl(c, ks, div_up(n, 256), 256, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
+                launch_pdl(c, ks, div_up(n, SETUP_THREADS), SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             if (!fp.nobin && !fp.slab_cap) {
@@ -339,8 +339,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
             // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
             const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;
             const TriRec* tile_recs = fp.slab_cap ? c->slab.p : c->recs.p;
-            if (depth_mode) launch_pdl(c, k_tile<true>, tgrid, 256, st, fp, bp, in, tile_recs, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
-            else            launch_pdl(c, k_tile<false>, tgrid, 256, st, fp, bp, in, tile_recs, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
+            auto kt = depth_mode ? k_tile<true, false> : ((fp.batched && b > 0) ? k_tile<false, true> : k_tile<false, false>);   // batches: depth off only
+            launch_pdl(c, kt, tgrid, 256, st, fp, bp, in, tile_recs, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
             c->launches++;
         }
     } else {

@@ -31,9 +31,16 @@ constexpr int SMALL_MAX = 8;         // direct path: clipped bbox at most SMALL_
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;        // per thread -> 2048 counters per CTA
 constexpr int TILE_BATCH = 16;
+#ifndef SR_SETUP_THREADS
+#define SR_SETUP_THREADS 256
+#endif       // k_setup CTA size.  Its warps are independent (all staging is per warp; no block barrier after the first
+             // instruction).  Measured: 128 threads +0.6 % on the 1M soup (finer release of registers when one warp
+             // walks a large triangle), -10 % on the 10M-triangle mesh of pixel-sized triangles (twice the CTA launches
+             // for threads that live a few hundred cycles); 64 threads worse on both.
 #ifndef SR_SETUP_MINB
-#define SR_SETUP_MINB 5
-#endif       // resident CTAs per SM asked of the binning k_setup variants
+#define SR_SETUP_MINB (5 * 256 / SR_SETUP_THREADS)
+#endif       // resident CTAs per SM asked of the binning k_setup variants (1280 threads: 47-48 registers)
+constexpr int SETUP_THREADS = SR_SETUP_THREADS;
 #ifndef SR_TILE_MINB
 #define SR_TILE_MINB 5
 #endif       // triangles per coverage batch in k_tile
@@ -230,7 +237,7 @@ struct XformIn {
     float fw, fh;
 };
 template <bool DEPTH, bool BIN, bool XFORM>
-__global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
+__global__ void __launch_bounds__(SETUP_THREADS, (BIN || DEPTH) ? SR_SETUP_MINB : 2048 / SETUP_THREADS) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
@@ -238,17 +245,17 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
     TL_BEGIN(status, 2 * bp.index);
     pdl_wait();
     TL_GO(status, 2 * bp.index);
-    __shared__ StagedTri s_tri[256];
-    __shared__ StagedRect s_rect[BIN ? 256 : 1];
-    __shared__ BaryT s_bt[DEPTH ? 256 : 1];
-    __shared__ float s_z[DEPTH ? 256 : 1][3];
-    __shared__ unsigned s_nsmall;
+    __shared__ StagedTri s_tri[SETUP_THREADS];
+    __shared__ StagedRect s_rect[BIN ? SETUP_THREADS : 1];
+    __shared__ BaryT s_bt[DEPTH ? SETUP_THREADS : 1];
+    __shared__ float s_z[DEPTH ? SETUP_THREADS : 1][3];
+    __shared__ unsigned s_tally;                            // (warps finished) << 16 | small triangles of the CTA
 
     const bool late = fp.batched && bp.index > 0;                   // only later batches can meet retired tiles
     if (late && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
     if (fp.batched && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&status->batches_run, 1u);
-    if (threadIdx.x == 0) s_nsmall = 0;
-    __syncthreads();
+    if (threadIdx.x == 0) s_tally = 0;
+    __syncthreads();                                         // the only block barrier: all warps arrive together
 
     const int prim = bp.lo + blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
@@ -346,7 +353,6 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
     unsigned base = 0;
     if (lane == 0) {
         if (m_skip) atomicAdd(&status->domain_skipped, __popc(m_skip));
-        if (m_small | m_tiny) atomicAdd(&s_nsmall, __popc(m_small) + __popc(m_tiny));
         if (m_large) base = atomicAdd(&status->n_large[bp.index], __popc(m_large));
     }
     const int wbase = threadIdx.x & ~31;
@@ -477,8 +483,17 @@ __global__ void __launch_bounds__(256, (BIN || DEPTH) ? SR_SETUP_MINB : 8) k_set
             }
         });
     }
-    __syncthreads();
-    if (threadIdx.x == 0 && s_nsmall) atomicAdd(&status->n_small, s_nsmall);
+    // no barrier at the end (fast warps must not wait for one that bins a screen-sized triangle): the last warp to
+    // get here publishes the CTA's small-triangle count
+    // (one shared atomic carries both the warp's count and its "done" tick, so no ordering between two words is needed)
+    if (lane == 0) {
+        const unsigned mine = __popc(m_small) + __popc(m_tiny);
+        const unsigned before = atomicAdd(&s_tally, (1u << 16) | mine);
+        if ((before >> 16) == (unsigned)(SETUP_THREADS / 32 - 1)) {
+            const unsigned ns = (before & 0xffffu) + mine;
+            if (ns) atomicAdd(&status->n_small, ns);
+        }
+    }
     TL_END(status, 2 * bp.index);
 }
 
@@ -680,7 +695,7 @@ __device__ __forceinline__ void shade_pixel(const ShadeIn& in, unsigned prim, in
     bgra = pack_bgra(blend3(ca.x, cb.x, cc.x, w), blend3(ca.y, cb.y, cc.y, w), blend3(ca.z, cb.z, cc.z, w));  // R:266-268
 }
 
-template <bool DEPTH>
+template <bool DEPTH, bool LATE>          // LATE: a later batch of a batched frame (persistent grid, retired tiles are skipped)
 __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
                                               const unsigned* __restrict__ cursor, unsigned* __restrict__ counts,
                                               const unsigned* __restrict__ pairs, unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
@@ -702,7 +717,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
     const int j = tid >> TILE_SHIFT, row = tid & (TILE - 1);        // coverage role: (triangle j of the batch, row)
-    const bool late = fp.batched && bp.index > 0;                   // only later batches can meet retired tiles
+    constexpr bool late = LATE;                                     // only later batches can meet retired tiles
     if (DEPTH) {
 #pragma unroll
         for (int q = 0; q < NCHUNK - 1; ++q) if (tid == q) s_zord[q] = depth_ord(fp.zthr[q]);
@@ -711,9 +726,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         for (int w = blockIdx.x * blockDim.x + tid; w < fp.wpr * fp.tiles_y; w += gridDim.x * blockDim.x) fp.done_bits[w] = 0u;
     if (late && status->tiles_done >= (unsigned)fp.ntiles) { TL_END(status, 2 * bp.index + 1); return; }
 
-    // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA launches
-    for (int tile = blockIdx.x; tile < fp.ntiles; tile += gridDim.x) {
-    if (late && tile_done[tile] == fp.epoch) continue;              // retired by an earlier batch
+    auto do_tile = [&](const int tile) {
     int tx, ty;
     divmod_tiles(tile, fp.tiles_x, ty, tx);
     const int x = tx * TILE + px, y = ty * TILE + py;
@@ -922,8 +935,8 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             atomicAdd(&status->tiles_done, 1u);
         }
     }
-    if (!inside) continue;
-    if (!shade_now) { if (v != v_in) vis32[o] = v; continue; }      // park for the next batch
+    if (!inside) return;
+    if (!shade_now) { if (v != v_in) vis32[o] = v; return; }      // park for the next batch
     if (DEPTH) { if (k_in != SR_KEY_EMPTY) vis64[o] = SR_KEY_EMPTY; }   // re-arm the visibility word for the next frame
     else       { if (v_in) vis32[o] = 0u; }
     unsigned bgra = 0u;                                  // clear colour (R:205)
@@ -932,7 +945,30 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     else       { if (v) shade_pixel(in, v - 1u, x, y + fp.y_org, false, bgra, depth); }
     color_out[o] = bgra;
     if (depth_out) depth_out[o] = depth;
-    }   // tile loop
+    };   // do_tile
+    if (!LATE) {                                            // first (or only) batch: the grid has one CTA per tile
+        do_tile(blockIdx.x);
+    } else {
+        // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA
+        // launches; the flags of a CTA's next 32 tiles are fetched by warp 0 in ONE round trip (one dependent load per
+        // tile made the almost empty final batch of the 1M soup a chain of ~10 round trips: 70 % of its stall samples)
+        __shared__ unsigned s_open;
+        for (int g0 = blockIdx.x; g0 < fp.ntiles; g0 += 32 * (int)gridDim.x) {
+            __syncthreads();                               // s_open of the previous group has been read by everyone
+            if (tid < 32) {
+                const int t = g0 + tid * (int)gridDim.x;
+                const unsigned m = __ballot_sync(0xffffffffu, t < fp.ntiles && tile_done[t] != fp.epoch);   // retired by an earlier batch?
+                if (tid == 0) s_open = m;
+            }
+            __syncthreads();
+            unsigned open_mask = s_open;
+            while (open_mask) {
+                const int tile = g0 + (__ffs(open_mask) - 1) * (int)gridDim.x;
+                open_mask &= open_mask - 1u;
+                do_tile(tile);
+            }
+        }
+    }
     TL_END(status, 2 * bp.index + 1);
 }
 
