@@ -111,6 +111,17 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def bind_to_gpu_numa_node(index: int) -> None:
+    """N ranks on one box: run this rank on the CPUs next to its GPU, so that the pinned host images of the e2e leg
+    (first touch) and the PCIe writes into them stay on the GPU's own socket.  Best effort."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(index))
+    except Exception:
+        pass
+
+
 def cpu_count() -> int:
     try:
         return len(os.sched_getaffinity(0))
@@ -194,6 +205,7 @@ def run_cuda(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        bind_to_gpu_numa_node(local)
 
     desc, W, H, v, i, xf = make_workload(args.workload)
     ntris, nverts = i.size // 3, int(v.shape[0])
@@ -252,27 +264,41 @@ def run_cuda(args):
     for k in range(max(3, Wm)):
         rp.transform = xf(frame0 + k)
         r.render(rp)
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for k in range(K):
-        rp.transform = xf(frame0 + Wm + k)
-        r.render(rp)
-    t_sync = max_over_ranks(time.perf_counter() - t0, device=dev)
-    e2e_sync = world * K / t_sync
+
+    def timed_passes(one_pass):
+        """The K e2e frames are repeated until the wall-clock region is ~0.3 s (a 1080p frame takes 0.3 ms, a 512x512
+        view 0.05 ms: K = 100 frames alone would be a region of a few ms, at the mercy of one scheduler hiccup on
+        one of N ranks).  Returns whole-job frames/s (max over ranks of the wall time) and the pass count."""
+        t0 = time.perf_counter()
+        one_pass()
+        passes = int(min(200, max(1, np.ceil(0.3 / max(time.perf_counter() - t0, 1e-4)))))
+        passes = int(max_over_ranks(float(passes), device=dev))          # the same count on every rank
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(passes):
+            one_pass()
+        t = max_over_ranks(time.perf_counter() - t0, device=dev)
+        return world * K * passes / t, passes
+
+    def sync_pass():
+        for k in range(K):
+            rp.transform = xf(frame0 + Wm + k)
+            r.render(rp)
+
+    e2e_sync, sync_passes = timed_passes(sync_pass)
     CH = 16
     bc = torch.empty((CH, H, W, 4), dtype=torch.uint8).pin_memory()
     bd = torch.empty((CH, H, W), dtype=torch.float32).pin_memory()
     mats = np.stack([xf(frame0 + Wm + k) for k in range(K)])
     r.render_views(mats[:min(K, CH)], W, H, color_out=bc.numpy(), depth_out=bd.numpy())      # warm-up
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for s0 in range(0, K, CH):
-        n = min(CH, K - s0)
-        r.render_views(mats[s0:s0 + n], W, H, color_out=bc.numpy()[:n], depth_out=bd.numpy()[:n])
-    t_e2e = max_over_ranks(time.perf_counter() - t0, device=dev)
-    e2e_value = world * K / t_e2e
+
+    def batch_pass():
+        for s0 in range(0, K, CH):
+            n = min(CH, K - s0)
+            r.render_views(mats[s0:s0 + n], W, H, color_out=bc.numpy()[:n], depth_out=bd.numpy()[:n])
+
+    e2e_value, batch_passes = timed_passes(batch_pass)
 
     line = None
     if rank == 0:
@@ -340,7 +366,9 @@ def run_cuda(args):
                                        f"frame; host has {cpu_count()} cores"},
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": 8 * W * H,
                     "api": "sr_render_batch, 16 frames per call, pinned host images, mesh uploaded once by sr_set_mesh",
-                    "sync_per_frame": {"value": e2e_sync, "unit": "frames/s", "api": "sr_render, one synchronous call per frame"}},
+                    "frames_timed_per_rank": K * batch_passes,
+                    "sync_per_frame": {"value": e2e_sync, "unit": "frames/s", "api": "sr_render, one synchronous call per frame",
+                                       "frames_timed_per_rank": K * sync_passes}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "wall_s_timed_region": t_wall,
