@@ -808,6 +808,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         __pipeline_wait_prior(0);
     }
     int cur = 0;
+    bool all_final = false;                                // depth off: the list was left early, every pixel holds its final index
     __syncthreads();                                       // s_rec[0] complete
 
     while (p < end) {
@@ -873,11 +874,22 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                     if (l <= r) mask = ((2u << (r - l)) - 1u) << (l - x_lo);
                 }
             }
+            // Depth off: the round's triangles are filed by DESCENDING index (rank = how many of the round have a
+            // higher index; a tile list holds a triangle once, so ranks are a permutation), in the column whose bit
+            // comes out at position `rank` of the gathered word below: the winner of a pixel is then its lowest set
+            // bit, one step instead of a loop over every covering triangle (max is order independent: same image).
+            int col = j;
+            if (!DEPTH) {
+                const unsigned mine = s_rec[cur][j].prim;
+                const unsigned higher = __ballot_sync(0xffffffffu, row < n && s_rec[cur][row].prim > mine);
+                const int rank = j < n ? __popc((higher >> (tid & 16)) & 0xffffu) : j;      // j >= n: the unused ranks
+                col = ((rank & 7) << 1) | (rank >> 3);     // ranks 0..7 -> bits 0..7, ranks 8..15 -> bits 16..23
+            }
             if (j < n && row == 0) {
-                s_prim[j] = s_rec[cur][j].prim;
+                s_prim[col] = s_rec[cur][j].prim;
                 if (DEPTH && culled) ++n_culled;
             }
-            s_mask[row][j] = (unsigned short)mask;         // zero for j >= n
+            s_mask[row][col] = (unsigned short)mask;       // zero for j >= n
         }
         __syncthreads();
         {   // phase B: each pixel gathers "which triangles of the batch cover me" into one word (two triangles per
@@ -888,16 +900,19 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             unsigned bits = 0;
 #pragma unroll
             for (int q = 0; q < 8; ++q) bits |= ((mw[q] >> px) & 0x00010001u) << q;
-            while (bits) {
-                const int b = __ffs(bits) - 1;
-                bits &= bits - 1;
-                const int jj = ((b & 15) << 1) | (b >> 4);
-                if (DEPTH) {
+            if (!DEPTH) {
+                if (bits) {                                // lowest set bit = highest index of the round (see phase A)
+                    const int b = __ffs(bits) - 1;
+                    v = max(v, s_prim[((b & 15) << 1) | (b >> 4)] + 1u);
+                }
+            } else {
+                while (bits) {
+                    const int b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const int jj = ((b & 15) << 1) | (b >> 4);
                     const float3 w = bary_weights(s_bt[jj], x, y + fp.y_org);
                     const float d = blend3(s_z[jj][0], s_z[jj][1], s_z[jj][2], w);
                     if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[jj]));
-                } else {
-                    v = max(v, s_prim[jj] + 1u);
                 }
             }
         }
@@ -909,9 +924,11 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             __syncthreads();
         } else {
             // every remaining pair of this batch has prim < thr (chunks are stored in descending order)
-            const unsigned thr = (unsigned)bp.lo + ((((s_prim[n - 1] - (unsigned)bp.lo) >> bp.chunk_shift) + 1u) << bp.chunk_shift);
+            // (the round's lowest index, rank n - 1, sits in the chunk of the round's last record: chunks are monotone in the index)
+            const unsigned low = s_prim[(((n - 1) & 7) << 1) | ((n - 1) >> 3)];
+            const unsigned thr = (unsigned)bp.lo + ((((low - (unsigned)bp.lo) >> bp.chunk_shift) + 1u) << bp.chunk_shift);
             const bool final_px = !inside || v > thr;    // v - 1 >= thr
-            if (__syncthreads_and(final_px)) break;
+            if (__syncthreads_and(final_px)) { all_final = true; break; }
         }
     }
     __pipeline_wait_prior(0);
@@ -928,7 +945,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     bool shade_now = true;
     if (fp.batched && !bp.final_batch) {
         // a pixel covered by this or an earlier batch cannot be changed by later (lower-index) batches
-        shade_now = __syncthreads_and(!inside || v != 0u) != 0;
+        shade_now = all_final || __syncthreads_and(!inside || v != 0u) != 0;    // all_final (block-uniform): v > thr >= 0 everywhere
         if (shade_now && tid == 0) {
             tile_done[tile] = fp.epoch;
             atomicOr(&fp.done_bits[ty * fp.wpr + (tx >> 5)], 1u << (tx & 31));
