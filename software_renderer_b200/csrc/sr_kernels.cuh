@@ -42,8 +42,9 @@ constexpr int TILE_BATCH = 16;
 #endif       // resident CTAs per SM asked of the binning k_setup variants (1280 threads: 47-48 registers)
 constexpr int SETUP_THREADS = SR_SETUP_THREADS;
 #ifndef SR_TILE_MINB
-#define SR_TILE_MINB 5
-#endif       // triangles per coverage batch in k_tile
+#define SR_TILE_MINB 6
+#endif       // resident CTAs per SM asked of the depth-off k_tile (40 registers, 12 bytes of spill).  Measured with the
+             // rank-ordered rounds: 5 CTAs 6070 / 16040 frames/s (soup1m / ico80k), 6 CTAs 6190 / 16320, 8 CTAs 6110 / 15380
 
 // Per-view counters, read back by the host after the frame.
 struct ViewStatus {
