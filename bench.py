@@ -129,7 +129,7 @@ def cpu_count() -> int:
         return os.cpu_count() or 1
 
 
-def time_oracle(v, i, xf, W, H, nthreads: int, frames_per_thread: int, stride: int):
+def time_oracle(v, i, xf, W, H, nthreads: int, frames_per_thread: int, stride: int, depth_test: bool = False):
     """Runs the oracle on `nthreads` host threads, each rendering `frames_per_thread` samples (every `stride`-th
     triangle of the frame).  Returns seconds of wall time."""
     from oracle import oracle as O
@@ -139,7 +139,8 @@ def time_oracle(v, i, xf, W, H, nthreads: int, frames_per_thread: int, stride: i
 
     def work(t):
         for f in range(frames_per_thread):
-            O.render(v, idx, xf(t * frames_per_thread + f), W, H, color_out=bufs[t][0], depth_out=bufs[t][1])
+            O.render(v, idx, xf(t * frames_per_thread + f), W, H, flags=O.DEPTH_LESS if depth_test else 0,
+                     color_out=bufs[t][0], depth_out=bufs[t][1])
 
     th = [threading.Thread(target=work, args=(t,)) for t in range(nthreads)]
     t0 = time.perf_counter()
@@ -162,17 +163,17 @@ def run_reference(args):
     O.lib()
     # calibrate: one thread, a 1/64 sample of one frame
     stride0 = 64 if ntris >= 64_000 else 1
-    t_cal = time_oracle(v, i, xf, W, H, 1, 1, stride0)
+    t_cal = time_oracle(v, i, xf, W, H, 1, 1, stride0, bool(args.depth_test))
     full_frame_s = t_cal * stride0                       # estimate; cost is ~linear in triangles for these meshes
     budget = 150.0 / max(1, args.steps + args.warmup)    # seconds per step
     stride = 1
     while full_frame_s / stride > budget and ntris // (stride * 2) >= 1000:
         stride *= 2
     for _ in range(args.warmup):
-        time_oracle(v, i, xf, W, H, cores, 1, stride)
+        time_oracle(v, i, xf, W, H, cores, 1, stride, bool(args.depth_test))
     t = 0.0
     for _ in range(args.steps):
-        t += time_oracle(v, i, xf, W, H, cores, 1, stride)
+        t += time_oracle(v, i, xf, W, H, cores, 1, stride, bool(args.depth_test))
     # each step renders `cores` samples, each 1/stride of a frame's triangles (plus a full clear)
     frames = args.steps * cores / stride
     value = frames / t
@@ -182,7 +183,9 @@ def run_reference(args):
         "impl": "reference", "metric": "frames_per_second", "value": value, "unit": "frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * t / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+i64", "data": "synthetic",
-        "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": int(v.shape[0])},
+        "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": int(v.shape[0]),
+                   "depth_test": bool(args.depth_test), "l2": "n/a (host cores)",
+                   "parallelism": f"{cores} host threads, one render pass each per step"},
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -335,13 +338,13 @@ def run_cuda(args):
         # CPU baseline: the oracle on one host core (the reference loop is sequential, Renderer.swift:222), about 10 s
         # of CPU work: calibrate on a 1/8 sample, then whole frames (or the largest 1/stride sample that fits)
         stride0 = 8 if ntris >= 500_000 else 1
-        t_cal = time_oracle(v, i, xf, W, H, 1, 1, stride0)
+        t_cal = time_oracle(v, i, xf, W, H, 1, 1, stride0, bool(args.depth_test))
         full_s = t_cal * stride0
         stride = 1
         while full_s / stride > 15.0:
             stride *= 2
         nframes = int(max(1, min(2000, 10.0 / max(full_s / stride, 1e-4))))
-        t_cpu = time_oracle(v, i, xf, W, H, 1, nframes, stride)
+        t_cpu = time_oracle(v, i, xf, W, H, 1, nframes, stride, bool(args.depth_test))
         cpu_value = (nframes / stride) / t_cpu
         line = {
             "metric": "frames_per_second", "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
