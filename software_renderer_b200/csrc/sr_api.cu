@@ -466,6 +466,26 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
     }
 }
 
+// Debug build (-DSR_TIMELINE): one line per view with the overlapped per-launch timeline the kernels stamped into the
+// status words (first CTA started, first CTA past the grid dependency, last CTA done), in µs from the frame's start.
+void print_timeline(const sr_ctx* c, size_t nviews) {
+#ifdef SR_TIMELINE
+    for (size_t v = 0; v < nviews; ++v) {
+        const ViewStatus& s = c->h_status[v];
+        unsigned long long t0 = ~0ull;
+        for (int k = 0; k < 2 * MAX_BATCHES; ++k) if (s.tl_launch_inv[k]) t0 = std::min(t0, ~s.tl_launch_inv[k]);
+        fprintf(stderr, "view %zu:", v);
+        for (int k = 0; k < 2 * MAX_BATCHES; ++k)
+            if (s.tl_launch_inv[k])
+                fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
+                        (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
+        fprintf(stderr, "\n");
+    }
+#else
+    (void)c; (void)nviews;
+#endif
+}
+
 void finish_profile(sr_ctx* c) {
     if (!c->profiling) return;
     for (int i = 0; i + 1 < c->prof_n; ++i) cudaEventElapsedTime(&c->prof_ms[i], c->prof_ev[i], c->prof_ev[i + 1]);
@@ -487,19 +507,7 @@ int finish_pending(sr_ctx* c) {
             if (rc) return rc;
         }
     }
-#ifdef SR_TIMELINE
-    for (size_t v = 0; v < nviews; ++v) {
-        const ViewStatus& s = c->h_status[v];
-        unsigned long long t0 = ~0ull;
-        for (int k = 0; k < 2 * MAX_BATCHES; ++k) if (s.tl_launch_inv[k]) t0 = std::min(t0, ~s.tl_launch_inv[k]);
-        fprintf(stderr, "view %zu:", v);
-        for (int k = 0; k < 2 * MAX_BATCHES; ++k)
-            if (s.tl_launch_inv[k])
-                fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
-                        (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
-        fprintf(stderr, "\n");
-    }
-#endif
+    print_timeline(c, nviews);
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
     c->stats.gpu_ms = ms;
@@ -737,19 +745,7 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
             if (want_depth && !early_depth) SR_CUDA(c, cudaMemcpyAsync(depth + npx * i, c->out_depth[0].p, npx * sizeof(float), cudaMemcpyDeviceToHost, st));
         }
     }
-#ifdef SR_TIMELINE
-    for (size_t v = 0; v < nviews; ++v) {
-        const ViewStatus& s = c->h_status[v];
-        unsigned long long t0 = ~0ull;
-        for (int k = 0; k < 2 * MAX_BATCHES; ++k) if (s.tl_launch_inv[k]) t0 = std::min(t0, ~s.tl_launch_inv[k]);
-        fprintf(stderr, "view %zu:", v);
-        for (int k = 0; k < 2 * MAX_BATCHES; ++k)
-            if (s.tl_launch_inv[k])
-                fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
-                        (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
-        fprintf(stderr, "\n");
-    }
-#endif
+    print_timeline(c, nviews);
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
     c->stats.gpu_ms = ms;

@@ -81,3 +81,36 @@ def test_rect_touched_never_drops_a_covered_tile():
                 kept += keep
                 pruned += not keep
     assert pruned > 0.2 * (kept + pruned)
+
+
+def test_rank_ordered_round_of_the_tile_kernel():
+    """csrc/sr_kernels.cuh::k_tile, depth off, restated with Python ints: the 16 triangles of a round are filed by
+    descending primitive index (rank = how many of the round have a higher index) in column ((rank & 7) << 1) |
+    (rank >> 3) of the 16 x 16-bit row masks; a pixel gathers bit q from the low half of word q and bit 16 + q from
+    its high half, and takes the LOWEST set bit as the winner.  For random rounds (any length, any coverage) that
+    must be the highest covering index — the outcome of the sequential loop Renderer.swift:221-229 with the
+    unconditional store of R:268 — and the early-out threshold must come from the round's lowest index."""
+    rng = np.random.default_rng(11)
+    for _ in range(3000):
+        n = int(rng.integers(1, 17))
+        prims = rng.choice(1 << 20, size=n, replace=False)              # a tile list holds a triangle once
+        cover = rng.random(n) < rng.random()                            # which triangles cover the pixel
+        col_mask = np.zeros(16, dtype=np.int64)                         # one pixel: bit 0 of each column's row mask
+        s_prim = np.full(16, -1, dtype=np.int64)
+        for j in range(16):
+            rank = int((prims > prims[j]).sum()) if j < n else j
+            col = ((rank & 7) << 1) | (rank >> 3)
+            assert col_mask[col] == 0 and (j >= n or s_prim[col] == -1)  # ranks are a permutation: no column is shared
+            if j < n:
+                s_prim[col] = prims[j]
+                col_mask[col] = int(cover[j])
+        words = [(int(col_mask[2 * q]) | (int(col_mask[2 * q + 1]) << 16)) for q in range(8)]
+        bits = 0
+        for q in range(8):
+            bits |= (words[q] & 0x00010001) << q
+        if cover.any():
+            b = (bits & -bits).bit_length() - 1
+            assert s_prim[((b & 15) << 1) | (b >> 4)] == prims[cover].max()
+        else:
+            assert bits == 0
+        assert s_prim[(((n - 1) & 7) << 1) | ((n - 1) >> 3)] == prims.min()
