@@ -176,12 +176,12 @@ __device__ __forceinline__ bool tile_retired(const FrameParams& fp, int tx, int 
 // any tile of row `ty`, columns [txa, txb], still open?
 __device__ __forceinline__ bool row_has_open(const FrameParams& fp, int ty, int txa, int txb) {
     const unsigned* row = fp.done_bits + ty * fp.wpr;
-    for (int w = txa >> 5; w <= (txb >> 5); ++w) {
-        const int lo = max(txa - (w << 5), 0), hi = min(txb - (w << 5), 31);
-        const unsigned mask = (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
-        if (~__ldg(&row[w]) & mask) return true;
-    }
-    return false;
+    const int wa = txa >> 5, wb = txb >> 5;
+    const unsigned first = 0xffffffffu << (txa & 31), last = 0xffffffffu >> (31 - (txb & 31));
+    if (wa == wb) return (~__ldg(&row[wa]) & first & last) != 0u;      // the usual case: the columns sit in one word
+    if (~__ldg(&row[wa]) & first) return true;
+    for (int w = wa + 1; w < wb; ++w) if (~__ldg(&row[w])) return true;
+    return (~__ldg(&row[wb]) & last) != 0u;
 }
 struct BatchParams {
     int lo, hi;               // primitive range [lo, hi) of this batch

@@ -114,3 +114,29 @@ def test_rank_ordered_round_of_the_tile_kernel():
         else:
             assert bits == 0
         assert s_prim[(((n - 1) & 7) << 1) | ((n - 1) >> 3)] == prims.min()
+
+
+def test_row_has_open_bit_logic():
+    """csrc/sr_kernels.cuh::row_has_open (retired-tile bitmap, one bit per tile, 32 tiles per word) restated with
+    Python ints against the definition: some tile column in [txa, txb] has its 'done' bit clear."""
+    rng = np.random.default_rng(5)
+    M = 0xFFFFFFFF
+    for _ in range(20000):
+        ncols = int(rng.integers(1, 200))
+        wpr = (ncols + 31) // 32
+        density = rng.choice([0.0, 0.5, 0.97, 1.0])
+        done = rng.random(ncols) < density
+        words = [0] * wpr
+        for tx in range(ncols):
+            if done[tx]:
+                words[tx >> 5] |= 1 << (tx & 31)
+        txa = int(rng.integers(0, ncols))
+        txb = int(rng.integers(txa, ncols))
+        wa, wb = txa >> 5, txb >> 5
+        first, last = (M << (txa & 31)) & M, M >> (31 - (txb & 31))
+        if wa == wb:
+            got = ((~words[wa]) & M & first & last) != 0
+        else:
+            got = ((~words[wa]) & M & first) != 0 or any(((~words[w]) & M) != 0 for w in range(wa + 1, wb)) \
+                or ((~words[wb]) & M & last) != 0
+        assert got == (not done[txa:txb + 1].all())
