@@ -174,3 +174,35 @@ def test_image_writers_roundtrip(tmp_path):
         pos += 12 + n
     rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(7, 1 + 5 * 4)
     assert (rows[:, 0] == 0).all() and np.array_equal(rows[:, 1:].reshape(7, 5, 4), img[..., [2, 1, 0, 3]])
+
+
+def test_span_rule_is_invariant_under_row_shifts_but_weights_are_not():
+    """The claim behind sr_set_band (screen-band split): interpolate (R:467-494) uses only differences of y, so moving
+    the truncated corners AND the row by the same integer leaves every span end unchanged (both restatements: the
+    C++ oracle and the pure-Python reading); ws(xy:) (R:88-100) is float arithmetic on Float(Int) + 0.5, which is
+    NOT shift invariant for far off-screen corners, which is why the kernels shade in frame rows."""
+    from oracle import literal_py as L
+    rng = np.random.default_rng(21)
+    moved = 0
+    for _ in range(400):
+        big = rng.random() < 0.3
+        lim = (1 << 29) if big else 3000
+        pts = rng.integers(-lim, lim, size=(3, 2))
+        pts = pts[np.argsort(pts[:, 1], kind="stable")]              # sorted by y like R:271 leaves them
+        shift = int(rng.integers(1, 2200))
+        shifted = pts - np.array([0, shift])
+        for vals in (pts, pts[[0, 2]]):                              # left = [s0, s1, s2], right = [s0, s2] (R:272-273)
+            sv = vals - np.array([0, shift])
+            for t in rng.integers(int(pts[0, 1]), int(pts[2, 1]) + 1, size=6):
+                want = O.interpolate(vals, int(t))
+                assert want == O.interpolate(sv, int(t) - shift)
+                assert want == L.interpolate([tuple(map(int, p)) for p in vals], int(t))
+                assert want == L.interpolate([tuple(map(int, p)) for p in sv], int(t) - shift)
+        x, y = int(rng.integers(0, 1920)), int(rng.integers(shift, shift + 1080))
+        w0 = O.weights(pts, x, y)
+        w1 = O.weights(shifted, x, y - shift)
+        if big and not np.array_equal(w0.view(np.uint32), w1.view(np.uint32)):
+            moved += 1
+        if not big:                                                  # on-screen magnitudes: every Float(Int) + 0.5 is exact
+            assert np.array_equal(w0.view(np.uint32), w1.view(np.uint32))
+    assert moved > 0
