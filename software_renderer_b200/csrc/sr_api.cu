@@ -77,6 +77,7 @@ struct sr_ctx {
     double first_frac = 0.125;           // batched frames: share of the primitives (from the top) in the first batch
     int force_batches = -1;              // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     bool use_pdl = true;
+    bool use_compact = true;             // SR_COMPACT=0: late batches run the one-triangle-per-thread k_setup
     // speculative frames without the binning kernels: enabled after a frame in which no triangle was large; a frame
     // that does meet a large triangle only counts it and is re-run with the full pipeline (results identical)
     bool nobin_mode = false, call_nobin = false, allow_nobin = true;   // SR_NOBIN=0 disables
@@ -306,11 +307,15 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
             while (n > 0 && ((n - 1) >> bp.chunk_shift) >= NCHUNK) bp.chunk_shift++;
             if (n > 0) {
                 prof_mark(c, st, "k_setup");
+                // later batches of a batched frame mostly meet retired tiles: the compacting variant (cheap test first,
+                // full setup on the survivors with dense warps)
+                const bool compact = fp.batched && b > 0 && c->use_compact;
                 auto ks = depth_mode ? (fp.nobin ? k_setup<true, false, false> : k_setup<true, true, false>)
                                      : (fp.nobin ? k_setup<false, false, false>
-                                                 : (fp.batched ? k_setup<false, true, true> : k_setup<false, true, false>));
+                                                 : (fp.batched ? (compact ? k_setup<false, true, true, true> : k_setup<false, true, true>)
+                                                               : k_setup<false, true, false>));
                 XformIn xf{c->pos.p, M, (float)W, (float)Hframe};
-                launch_pdl(c, ks, div_up(n, SETUP_THREADS), SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
+                launch_pdl(c, ks, div_up(n, compact ? SETUP_THREADS * LATE_PT : SETUP_THREADS), SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             if (!fp.nobin && !fp.slab_cap) {
@@ -536,6 +541,7 @@ int sr_create(sr_ctx** out, int device) {
     sr_ctx* c = new sr_ctx();
     c->device = device;
     if (const char* e = getenv("SR_PDL")) c->use_pdl = atoi(e) != 0;
+    if (const char* e = getenv("SR_COMPACT")) c->use_compact = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB")) c->slab_mode = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB_CAP")) c->slab_cap = std::max(1, atoi(e));
     if (const char* e = getenv("SR_NOBIN")) c->allow_nobin = atoi(e) != 0;
