@@ -177,6 +177,27 @@ void launch_pdl(sr_ctx* c, void (*kernel)(KArgs...), unsigned grid, unsigned blo
 
 int primitive_vertices(int prim) { return prim == SR_LINE ? 2 : 3; }   // R:179-188
 
+// Every kernel of a frame asks for the SAME shared-memory carve-out of the unified L1/shared array.  Left to the
+// driver's per-kernel choice, k_setup (24 KB per CTA, five CTAs) and k_tile (3 KB per CTA) get different splits: an SM
+// cannot hold CTAs of two configurations at once, so the dependent kernel's CTAs cannot move in while the previous
+// kernel drains (programmatic dependent launch is then void) and every kernel boundary costs a reconfiguration:
+// 7-8 us between kernels measured with the %globaltimer timeline, against 0.8-1 us for equal configurations
+// (tools/micro/pdl_gap.cu).  SR_CARVEOUT = percent of the array given to shared memory, -1 = driver default.
+template <class K>
+void set_carveout(K kernel, int pct) { cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct); }
+void set_frame_carveouts(int pct) {
+    if (pct < 0) return;
+    set_carveout(k_transform, pct);
+    set_carveout(k_setup<true, false, false>, pct);  set_carveout(k_setup<true, true, false>, pct);
+    set_carveout(k_setup<false, false, false>, pct); set_carveout(k_setup<false, true, false>, pct);
+    set_carveout(k_setup<false, true, true>, pct);   set_carveout(k_setup<false, true, true, true>, pct);
+    set_carveout(k_scan, pct); set_carveout(k_bin_fill, pct);
+    set_carveout(k_tile<true, false>, pct); set_carveout(k_tile<false, false>, pct); set_carveout(k_tile<false, true>, pct);
+    set_carveout(k_resolve<true, 1>, pct); set_carveout(k_resolve<true, 4>, pct);
+    set_carveout(k_resolve<false, 1>, pct); set_carveout(k_resolve<false, 4>, pct);
+    set_carveout(k_points_scatter, pct); set_carveout(k_points_resolve, pct); set_carveout(k_clear_depth, pct);
+}
+
 // Buffers of the compact-list fallback: one record per triangle and the pair array (grown on demand by re-runs).
 int ensure_compact(sr_ctx* c) {
     const size_t ntris = c->nidx / 3;
@@ -541,6 +562,12 @@ int sr_create(sr_ctx** out, int device) {
     sr_ctx* c = new sr_ctx();
     c->device = device;
     if (const char* e = getenv("SR_PDL")) c->use_pdl = atoi(e) != 0;
+    {
+        int pct = 57;                     // 146 KB of 256: five 24.5-KB k_setup CTAs (+1 KB each) fit
+        if (const char* e = getenv("SR_CARVEOUT")) pct = atoi(e);
+        set_frame_carveouts(pct);
+        cudaGetLastError();
+    }
     if (const char* e = getenv("SR_COMPACT")) c->use_compact = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB")) c->slab_mode = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB_CAP")) c->slab_cap = std::max(1, atoi(e));

@@ -45,6 +45,9 @@ constexpr int SETUP_THREADS = SR_SETUP_THREADS;
 #define SR_LATE_PT 4
 #endif       // triangles per thread in phase 1 of the compacting (late-batch) k_setup
 constexpr int LATE_PT = SR_LATE_PT;
+#ifndef SR_LATE_MINB
+#define SR_LATE_MINB SR_SETUP_MINB
+#endif
 #ifndef SR_TILE_MINB
 #define SR_TILE_MINB 6
 #endif       // resident CTAs per SM asked of the depth-off k_tile (40 registers, 12 bytes of spill).  Measured with the
@@ -247,7 +250,7 @@ struct XformIn {
 // the list with dense warps.  Without it every warp that holds ONE survivor walks the whole binning path with 31 idle
 // lanes (48 % of the warps at a 2 % survival rate).  Results are identical: visibility is max(index), list order free.
 template <bool DEPTH, bool BIN, bool XFORM, bool COMPACT = false>
-__global__ void __launch_bounds__(SETUP_THREADS, (BIN || DEPTH) ? SR_SETUP_MINB : 2048 / SETUP_THREADS) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
+__global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN || DEPTH) ? SR_SETUP_MINB : 2048 / SETUP_THREADS)) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
