@@ -48,12 +48,19 @@ typedef enum sr_status {
     SR_ERR_INDEX = -2,   /* an index is negative or >= nverts (reference: array trap, R:226) */
     SR_ERR_DOMAIN = -3,  /* >=1 primitive skipped: corner outside the valid domain (reference: trap, R:251) */
     SR_ERR_CUDA = -4,    /* CUDA runtime failure, or no device; see sr_last_error */
-    SR_ERR_NOMESH = -5   /* render called before sr_set_mesh */
+    SR_ERR_NOMESH = -5,  /* render called before sr_set_mesh */
+    SR_ERR_COMM = -6     /* sr_gather: NCCL missing / not initialised / failed; see sr_last_error */
 } sr_status;
 
 enum {
-    SR_FLAG_DEPTH_LESS = 1u << 0, /* run the depth test of R:257-261 (off = reference as shipped) */
-    SR_FLAG_NO_DEPTH_OUT = 1u << 1 /* do not produce / copy back the depth image (depth pointer may be NULL) */
+    SR_FLAG_DEPTH_LESS = 1u << 0,   /* run the depth test of R:257-261 (off = reference as shipped) */
+    SR_FLAG_NO_DEPTH_OUT = 1u << 1, /* do not produce / copy back the depth image (depth pointer may be NULL) */
+    /* Host-pointer calls with the depth test off: the pass leaves the depth image at the clear value +inf (R:206; the
+     * test that would write it is commented out, R:257-261).  With this flag the caller states that the depth image it
+     * passes still holds what the previous call of this context wrote there (same pointer, same size, not touched
+     * since): if that call left the cleared plane, the image is not written again.  Anything else (first call, another
+     * pointer or size, a depth-tested call in between) is detected and the plane is written as usual. */
+    SR_FLAG_DEPTH_UNTOUCHED = 1u << 2
 };
 
 /* Same bytes as Swift's Vertex (R:154-157). */
@@ -91,6 +98,20 @@ int sr_version(void);
  * (A:163); GpuRenderer caches its device buffers across frames (G:41-67).  Here the upload is explicit: call again
  * whenever the arrays change.  A trailing partial primitive is ignored, as R:221 does. */
 int sr_set_mesh(sr_ctx* ctx, const sr_vertex* vertices, size_t nverts, const int64_t* indices, size_t nidx);
+/* Generation counter of the uploaded mesh: incremented by every successful sr_set_mesh / sr_render_pass upload.  Host
+ * mirrors that cache a mesh key on it together with a caller-bumped version (see CudaRenderer.setMesh). */
+uint64_t sr_mesh_generation(const sr_ctx* ctx);
+
+/* -- host memory -------------------------------------------------------------------------------------------------
+ * The reference's caller owns the colour / depth images and the mesh arrays in ordinary memory (A:59-60, A:80-101,
+ * A:163).  Every call below accepts such pointers.  Page-locked memory lets the GPU's copy engines write / read it
+ * directly (about 3x the bandwidth of pageable memory on this box, profiles/): a host that wants that allocates its
+ * images and arrays here, or registers the ones it already has.  Alignment requirements: none for host pointers;
+ * device pointers (sr_render_device) need the natural alignment of their element (4 bytes). */
+int sr_host_alloc(sr_ctx* ctx, size_t bytes, void** out);
+int sr_host_free(sr_ctx* ctx, void* ptr);
+int sr_host_register(sr_ctx* ctx, void* ptr, size_t bytes);
+int sr_host_unregister(sr_ctx* ctx, void* ptr);
 
 /* -- render ---------------------------------------------------------------------------------------------------- */
 /* render(renderPass:) R:204-230 on the uploaded mesh: synchronous, writes host memory the caller owns
@@ -129,6 +150,31 @@ int sr_set_band(sr_ctx* ctx, int y0, int y1);
 
 /* Waits for the work enqueued by sr_render_device and returns its status (SR_OK / SR_ERR_DOMAIN / SR_ERR_CUDA). */
 int sr_sync(sr_ctx* ctx);
+
+/* -- composite: framebuffers of all ranks to one rank -------------------------------------------
+ * Views shard over one process per GPU with no exchange while rendering (R:204-230 keeps no cross-frame state).  When
+ * a composite is requested, each rank's finished framebuffers travel to `root` over NCCL (NVLink / NVSwitch) as
+ * grouped ncclSend / ncclRecv (NCCL has no gather primitive).  libnccl.so.2 is opened at run time (the copy the
+ * process already holds, e.g. PyTorch's, or the system one); without it these calls return SR_ERR_COMM.
+ *   sr_comm_unique_id   rank `root` of the job creates the 128-byte NCCL id; the host side hands it to the other ranks
+ *                       by whatever channel it has (torch.distributed / MPI / a file).
+ *   sr_comm_init        every rank: joins the communicator (collective call).
+ *   sr_gather           asynchronous: ordered after everything this context has enqueued so far on `after_stream` (NULL =
+ *                       the context's own stream), it runs on the context's gather stream, so the gather of one chunk
+ *                       of views overlaps the rendering of the next.  send_dev: this rank's block (device memory);
+ *                       recv_dev (root only): where the blocks land, rank r's at byte offset sum(bytes_per_rank[0..r));
+ *                       bytes_per_rank: `world` entries, identical on every rank.  `slot` (0..3) names the caller's
+ *                       buffer for sr_gather_fence.
+ *   sr_gather_fence     device-side: work enqueued on `stream` (NULL = own) after this call waits for the gather last
+ *                       issued with this slot — call it before rendering into a buffer a gather may still be reading.
+ *   sr_gather_sync      host-side: returns when every gather issued so far has completed. */
+int sr_comm_unique_id(void* id128_out);
+int sr_comm_init(sr_ctx* ctx, const void* id128, int rank, int world);
+int sr_comm_destroy(sr_ctx* ctx);
+int sr_gather(sr_ctx* ctx, const void* send_dev, void* recv_dev, const size_t* bytes_per_rank, int root, int slot,
+              void* after_stream);
+int sr_gather_fence(sr_ctx* ctx, int slot, void* stream);
+int sr_gather_sync(sr_ctx* ctx);
 
 /* Counters of the last completed render call. */
 int sr_get_stats(sr_ctx* ctx, sr_stats* out);

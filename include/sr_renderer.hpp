@@ -46,6 +46,10 @@ struct RenderPass {
     std::vector<int64_t> indices;                          // Swift [Int]
     PrimitiveType primitiveType = PrimitiveType::triangle;
     matrix_float4x4 transform;
+    // < 0 (default): the reference's contract - the arrays are handed over and uploaded on EVERY call (App.swift:163).
+    // >= 0: "static mesh" opt-in - uploaded when this number or the array sizes differ from the upload before; the
+    // caller bumps it after editing the arrays.  (Not a field of the reference's RenderPass.)
+    long long meshVersion = -1;
 };
 
 class CudaRenderer {
@@ -60,11 +64,17 @@ public:
 
     bool depthTest = false;                                // true: the test commented out at Renderer.swift:257-261
 
-    // Uploads the mesh of the pass (the reference hands the arrays over on every call, App.swift:163).
+    bool depthUntouched = false;                           // true: pass SR_FLAG_DEPTH_UNTOUCHED (see sr_cuda.h)
+
+    // Explicit upload (sr_set_mesh), for passes with a meshVersion.
     void setMesh(const std::vector<Vertex>& v, const std::vector<int64_t>& i) {
         check(sr_set_mesh(ctx_, reinterpret_cast<const sr_vertex*>(v.data()), v.size(), i.data(), i.size()));
-        mesh_v_ = v.data(); mesh_i_ = i.data(); mesh_nv_ = v.size(); mesh_ni_ = i.size();
+        mesh_version_ = -1;
     }
+
+    // Page-locked host memory for images and mesh arrays (sr_host_alloc); free with hostFree.
+    void* hostAlloc(size_t bytes) { void* p = nullptr; check(sr_host_alloc(ctx_, bytes, &p)); return p; }
+    void hostFree(void* p) { check(sr_host_free(ctx_, p)); }
 
     // Screen-band split of one frame: later render() calls write only rows [y0, y1) of the pass's images (bit-identical
     // to those rows of the whole frame); setBand(0, 0) returns to whole frames.
@@ -73,12 +83,27 @@ public:
     // render(renderPass:) — synchronous; writes colorBuffer and depthBuffer in place.  Returns the number of
     // primitives skipped by the domain rule (0 for every input the reference itself can render).
     uint64_t render(const RenderPass& rp) {
-        if (rp.vertices.data() != mesh_v_ || rp.indices.data() != mesh_i_ || rp.vertices.size() != mesh_nv_ || rp.indices.size() != mesh_ni_)
-            setMesh(rp.vertices, rp.indices);
         const size_t skip = static_cast<size_t>(band_y0_) * rp.colorBuffer.width;   // packed rows: a band is one block
-        int rc = sr_render(ctx_, &rp.transform.columns[0][0], static_cast<int>(rp.primitiveType), rp.colorBuffer.width,
-                           rp.colorBuffer.height, reinterpret_cast<uint8_t*>(rp.colorBuffer.pointer + skip), rp.depthBuffer.pointer + skip,
-                           depthTest ? SR_FLAG_DEPTH_LESS : 0u);
+        const uint32_t flags = (depthTest ? SR_FLAG_DEPTH_LESS : 0u) | (depthUntouched ? SR_FLAG_DEPTH_UNTOUCHED : 0u);
+        uint8_t* color = reinterpret_cast<uint8_t*>(rp.colorBuffer.pointer + skip);
+        float* depth = rp.depthBuffer.pointer + skip;
+        int rc;
+        if (rp.meshVersion < 0) {
+            // no guessing from addresses or sizes: the arrays travel with the call, like the reference's
+            mesh_version_ = -1;
+            rc = sr_render_pass(ctx_, reinterpret_cast<const sr_vertex*>(rp.vertices.data()), rp.vertices.size(), rp.indices.data(),
+                                rp.indices.size(), &rp.transform.columns[0][0], static_cast<int>(rp.primitiveType),
+                                rp.colorBuffer.width, rp.colorBuffer.height, color, depth, flags);
+        } else {
+            if (rp.meshVersion != mesh_version_ || rp.vertices.size() != mesh_nv_ || rp.indices.size() != mesh_ni_ ||
+                sr_mesh_generation(ctx_) != mesh_gen_) {
+                setMesh(rp.vertices, rp.indices);
+                mesh_version_ = rp.meshVersion; mesh_nv_ = rp.vertices.size(); mesh_ni_ = rp.indices.size();
+                mesh_gen_ = sr_mesh_generation(ctx_);
+            }
+            rc = sr_render(ctx_, &rp.transform.columns[0][0], static_cast<int>(rp.primitiveType), rp.colorBuffer.width,
+                           rp.colorBuffer.height, color, depth, flags);
+        }
         sr_stats st{};
         sr_get_stats(ctx_, &st);
         if (rc != SR_OK && rc != SR_ERR_DOMAIN) check(rc);
@@ -107,9 +132,9 @@ private:
         if (rc != SR_OK) throw std::runtime_error(std::string("libsr_cuda: ") + sr_last_error(ctx_) + " (" + std::to_string(rc) + ")");
     }
     sr_ctx* ctx_ = nullptr;
-    const void* mesh_v_ = nullptr;
-    const void* mesh_i_ = nullptr;
+    long long mesh_version_ = -1;
     size_t mesh_nv_ = 0, mesh_ni_ = 0;
+    uint64_t mesh_gen_ = 0;
     int band_y0_ = 0;
 };
 

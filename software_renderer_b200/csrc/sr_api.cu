@@ -4,11 +4,19 @@
 #include "sr_kernels.cuh"
 
 #include <algorithm>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
+
+#include <dlfcn.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 using namespace sr;
 
@@ -40,6 +48,126 @@ struct DevBuf {
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
+
+// Helper threads of a context for the host-side halves of the host-pointer calls: writing the constant +inf depth
+// plane of a pass that never tests depth (R:206; instead of shipping 4 bytes per pixel of a constant over PCIe) and
+// moving pageable caller memory through page-locked bounce buffers.  One job at a time, split evenly over the threads.
+class HostPool {
+public:
+    enum Kind { FILL_INF, COPY };
+    explicit HostPool(int n) : n_(n) {
+        for (int i = 0; i < n_; ++i) th_.emplace_back([this, i] { run(i); });
+    }
+    ~HostPool() {
+        { std::lock_guard<std::mutex> l(m_); stop_ = true; }
+        cv_job_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    int threads() const { return n_; }
+    void start(Kind kind, void* dst, const void* src, size_t bytes) {
+        if (n_ == 0) { part(Job{kind, dst, src, bytes}, 0, 1); return; }
+        {
+            std::unique_lock<std::mutex> l(m_);
+            cv_done_.wait(l, [&] { return pending_ == 0; });
+            job_ = Job{kind, dst, src, bytes};
+            pending_ = n_;
+            ++gen_;
+        }
+        cv_job_.notify_all();
+    }
+    void wait() {
+        if (n_ == 0) return;
+        std::unique_lock<std::mutex> l(m_);
+        cv_done_.wait(l, [&] { return pending_ == 0; });
+    }
+private:
+    struct Job { Kind kind; void* dst; const void* src; size_t bytes; };
+    static void part(const Job& j, int id, int n) {
+        // 64-byte aligned slices of [0, bytes)
+        const size_t per = ((j.bytes + n - 1) / n + 63) & ~(size_t)63;
+        const size_t lo = std::min(j.bytes, per * id), hi = std::min(j.bytes, per * (id + 1));
+        if (hi <= lo) return;
+        char* d = static_cast<char*>(j.dst) + lo;
+        if (j.kind == COPY) { std::memcpy(d, static_cast<const char*>(j.src) + lo, hi - lo); return; }
+        // +inf floats (R:206).  Streaming stores: the plane is written once and read by somebody else.
+        float* f = reinterpret_cast<float*>(d);
+        size_t cnt = (hi - lo) / sizeof(float), k = 0;
+        const float inf = __builtin_inff();
+#if defined(__SSE2__)
+        while (k < cnt && (reinterpret_cast<uintptr_t>(f + k) & 15)) f[k++] = inf;
+        const __m128 v = _mm_set1_ps(inf);
+        for (; k + 16 <= cnt; k += 16) {
+            _mm_stream_ps(f + k, v); _mm_stream_ps(f + k + 4, v); _mm_stream_ps(f + k + 8, v); _mm_stream_ps(f + k + 12, v);
+        }
+        _mm_sfence();
+#endif
+        for (; k < cnt; ++k) f[k] = inf;
+    }
+    void run(int id) {
+        unsigned long long seen = 0;
+        for (;;) {
+            Job j;
+            {
+                std::unique_lock<std::mutex> l(m_);
+                cv_job_.wait(l, [&] { return stop_ || gen_ != seen; });
+                if (stop_) return;
+                seen = gen_;
+                j = job_;
+            }
+            part(j, id, n_);
+            {
+                std::lock_guard<std::mutex> l(m_);
+                if (--pending_ == 0) cv_done_.notify_all();
+            }
+        }
+    }
+    int n_;
+    std::vector<std::thread> th_;
+    std::mutex m_;
+    std::condition_variable cv_job_, cv_done_;
+    Job job_{FILL_INF, nullptr, nullptr, 0};
+    unsigned long long gen_ = 0;
+    int pending_ = 0;
+    bool stop_ = false;
+};
+
+// NCCL, bound at run time (sr_gather): the library the process already holds (PyTorch's bundled copy) or the system's.
+struct Nccl {
+    typedef struct { char internal[128]; } UniqueId;
+    typedef void* Comm;
+    int (*GetUniqueId)(UniqueId*) = nullptr;
+    int (*CommInitRank)(Comm*, int, UniqueId, int) = nullptr;
+    int (*CommDestroy)(Comm) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int /*ncclDataType_t*/, int, Comm, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+    std::string why;
+    static Nccl& get() {
+        static Nccl n;
+        static std::once_flag once;
+        std::call_once(once, [] {
+            void* h = nullptr;
+            const char* names[] = {getenv("SR_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+            for (const char* nm : names) if (nm && !h) h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (!h) { n.why = "libnccl.so.2 not found (set SR_NCCL_LIB)"; return; }
+            auto sym = [&](const char* s) { void* p = dlsym(h, s); if (!p) n.why = std::string("missing NCCL symbol ") + s; return p; };
+            n.GetUniqueId = reinterpret_cast<decltype(n.GetUniqueId)>(sym("ncclGetUniqueId"));
+            n.CommInitRank = reinterpret_cast<decltype(n.CommInitRank)>(sym("ncclCommInitRank"));
+            n.CommDestroy = reinterpret_cast<decltype(n.CommDestroy)>(sym("ncclCommDestroy"));
+            n.GroupStart = reinterpret_cast<decltype(n.GroupStart)>(sym("ncclGroupStart"));
+            n.GroupEnd = reinterpret_cast<decltype(n.GroupEnd)>(sym("ncclGroupEnd"));
+            n.Send = reinterpret_cast<decltype(n.Send)>(sym("ncclSend"));
+            n.Recv = reinterpret_cast<decltype(n.Recv)>(sym("ncclRecv"));
+            n.GetErrorString = reinterpret_cast<decltype(n.GetErrorString)>(sym("ncclGetErrorString"));
+            n.ok = n.why.empty();
+        });
+        return n;
+    }
+};
+constexpr int kNcclUint8 = 1;      // ncclDataType_t: ncclInt8 0, ncclUint8 1 (nccl.h)
 
 }  // namespace
 
@@ -120,6 +248,26 @@ struct sr_ctx {
 
     sr_stats stats = {};
     uint64_t launches = 0;
+
+    // host-side helpers of the host-pointer calls
+    HostPool* pool = nullptr;            // SR_FILL_THREADS (default 4; 0 = constant depth plane crosses PCIe, pageable memory is left to the driver)
+    const void* last_depth_ptr = nullptr;   // SR_FLAG_DEPTH_UNTOUCHED: what the previous host call left in the caller's depth image
+    size_t last_depth_bytes = 0;
+    bool last_depth_cleared = false;
+    void* bounce[2] = {nullptr, nullptr};   // page-locked bounce buffers for pageable mesh arrays
+    cudaEvent_t ev_bounce[2] = {nullptr, nullptr};
+    DevBuf<uint8_t> mesh_stage;          // Swift-layout vertices + indices, converted on the device
+    unsigned long long* h_bad = nullptr; // pinned: first out-of-range index position
+    unsigned long long* d_bad = nullptr;
+    uint64_t mesh_generation = 0;
+    unsigned epoch0 = 0;                 // SR_EPOCH0 (tests): frame epoch a fresh tile_done array starts from
+
+    // composite gather (sr_gather)
+    Nccl::Comm comm = nullptr;
+    int comm_rank = -1, comm_world = 0;
+    cudaStream_t gather_stream = nullptr;
+    cudaEvent_t ev_gather_in = nullptr, ev_gather_done[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool gather_slot_used[4] = {false, false, false, false};
 };
 
 namespace {
@@ -221,7 +369,7 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
     if (tiles > c->tile_done.cap) {
         SR_CUDA(c, c->tile_done.reserve(tiles));
         SR_CUDA(c, cudaMemsetAsync(c->tile_done.p, 0, tiles * sizeof(unsigned), st));
-        c->frame_epoch = 0;
+        c->frame_epoch = c->epoch0;
     }
     const size_t nbits_words = div_up(div_up(W, TILE), 32) * div_up(H, TILE);
     if (nbits_words > c->done_bits.cap) {
@@ -298,7 +446,11 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
         fp.tiles_x = (int)div_up(W, TILE); fp.tiles_y = (int)div_up(H, TILE);
         fp.ntiles = fp.tiles_x * fp.tiles_y;
         fp.pair_capacity = (unsigned)std::min<size_t>(c->pairs.cap, 0xFFFFFFFFu);
-        fp.epoch = ++c->frame_epoch;
+        if (++c->frame_epoch == 0) {     // 2^32 frames: stamps of the previous cycle must not match the new epochs
+            SR_CUDA(c, cudaMemsetAsync(c->tile_done.p, 0, c->tile_done.cap * sizeof(unsigned), st));
+            c->frame_epoch = 1;
+        }
+        fp.epoch = c->frame_epoch;
         fp.batched = batched_frame ? 1 : 0;
         fp.done_bits = c->done_bits.p;
         fp.wpr = (int)div_up(fp.tiles_x, 32);
@@ -355,7 +507,12 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
             }
             if (fp.nobin) {
                 prof_mark(c, st, "k_resolve");
-                const bool wide = npx >= (4u << 20);       // four pixels per thread once that still fills the GPU
+                // four pixels per thread once that still fills the GPU; its 16-byte loads and stores need the view's first
+                // pixel on a 16-byte boundary in every plane (a view of a batch starts at a multiple of W*H elements; a
+                // caller's device pointer may be a slice)
+                const bool aligned16 = npx % 4 == 0 && (reinterpret_cast<uintptr_t>(color32) & 15) == 0 &&
+                                       (!depth_dev || (reinterpret_cast<uintptr_t>(depth_dev) & 15) == 0);
+                const bool wide = npx >= (4u << 20) && aligned16;
                 auto kr = depth_mode ? (wide ? k_resolve<true, 4> : k_resolve<true, 1>) : (wide ? k_resolve<false, 4> : k_resolve<false, 1>);
                 launch_pdl(c, kr, div_up(div_up(npx, wide ? 4 : 1), 256), 256, st, in, W, y_org, npx, c->vis32.p, c->vis64.p, color32, depth_dev);
                 c->launches++;
@@ -393,6 +550,11 @@ int check_args(sr_ctx* c, const float* transforms, size_t nviews, int prim, int 
     if (!transforms || !color || nviews == 0) return fail(c, SR_ERR_ARG, "null transform/colour pointer or zero views");
     if (!depth && !(flags & SR_FLAG_NO_DEPTH_OUT)) return fail(c, SR_ERR_ARG, "depth pointer is null without SR_FLAG_NO_DEPTH_OUT");
     if (W <= 0 || H <= 0 || (size_t)W * H > (1u << 30)) return fail(c, SR_ERR_ARG, "bad image size");
+    // what the packed fields of the binning kernels can represent: a bounding box's tile-column count lives in 15 bits
+    // (StagedRect.w), tile numbers go through a float-estimated division that is exact below 2^23 (divmod_tiles)
+    if ((W + TILE - 1) / TILE > 32767 || (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE) >= (1u << 23))
+        return fail(c, SR_ERR_ARG, "image too wide / too many 16x16 tiles for the binning kernels (width <= 524,272, tiles < 2^23)");
+    if (prim == SR_VERTICES && c->nidx > 0x7FFFFFF0ull) return fail(c, SR_ERR_ARG, "too many corners for SR_VERTICES (32-bit corner numbers)");
     if (c->band_y1 > H) return fail(c, SR_ERR_ARG, "the band set by sr_set_band ends below the image");
     if (prim < SR_TRIANGLE || prim > SR_VERTICES) return fail(c, SR_ERR_ARG, "unknown primitive type");
     if (!c->has_mesh) return fail(c, SR_ERR_NOMESH, "sr_set_mesh has not been called");
@@ -411,7 +573,8 @@ int collect_status(sr_ctx* c, size_t nviews, cudaStream_t st, std::vector<size_t
         const ViewStatus& s = c->h_status[i];
         unsigned most = 0;
         for (int b = 0; b < MAX_BATCHES; ++b) most = std::max(most, s.total_pairs[b]);
-        if (most > c->pairs.cap) { rerun->push_back(i); need = std::max(need, most); }
+        // compact lists only: slab frames have no pair array (their k_tile still tallies list lengths into total_pairs)
+        if (!c->call_slab_cap && !c->call_nobin && most > c->pairs.cap) { rerun->push_back(i); need = std::max(need, most); }
         else if (c->call_nobin && s.n_large[0] > 0) { rerun->push_back(i); c->stats.nobin_reruns++; }   // speculation failed
     }
     if (c->call_slab_cap) {
@@ -517,6 +680,33 @@ void finish_profile(sr_ctx* c) {
     for (int i = 0; i + 1 < c->prof_n; ++i) cudaEventElapsedTime(&c->prof_ms[i], c->prof_ev[i], c->prof_ev[i + 1]);
 }
 
+// Host -> device copy of caller memory.  Page-locked (sr_host_alloc / sr_host_register / cudaHostAlloc) memory is read by
+// the copy engine directly.  Pageable memory goes through two page-locked bounce buffers, filled by the helper threads
+// while the previous chunk is in flight (the driver's own staging of a pageable cudaMemcpyAsync is single-threaded).
+int upload(sr_ctx* c, void* dst_dev, const void* src, size_t bytes, cudaStream_t st) {
+    if (bytes == 0) return SR_OK;
+    cudaPointerAttributes at = {};
+    const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (pinned || !c->pool || c->pool->threads() == 0 || bytes < (1u << 20)) {
+        SR_CUDA(c, cudaMemcpyAsync(dst_dev, src, bytes, cudaMemcpyHostToDevice, st));
+        return SR_OK;
+    }
+    constexpr size_t kChunk = 8u << 20;
+    for (int b = 0; b < 2; ++b)
+        if (!c->bounce[b]) SR_CUDA(c, cudaHostAlloc(&c->bounce[b], kChunk, cudaHostAllocPortable));
+    int b = 0;
+    for (size_t off = 0; off < bytes; off += kChunk, b ^= 1) {
+        const size_t len = std::min(kChunk, bytes - off);
+        SR_CUDA(c, cudaEventSynchronize(c->ev_bounce[b]));          // the copy that last read this buffer is done
+        c->pool->start(HostPool::COPY, c->bounce[b], static_cast<const char*>(src) + off, len);
+        c->pool->wait();
+        SR_CUDA(c, cudaMemcpyAsync(static_cast<char*>(dst_dev) + off, c->bounce[b], len, cudaMemcpyHostToDevice, st));
+        SR_CUDA(c, cudaEventRecord(c->ev_bounce[b], st));
+    }
+    return SR_OK;
+}
+
 // Completes the pending device-output views: status read-back, overflow re-runs, stats.  Synchronises `st`.
 int finish_pending(sr_ctx* c) {
     auto& p = c->pending;
@@ -527,6 +717,7 @@ int finish_pending(sr_ctx* c) {
         int rc = collect_status(c, nviews, st, &rerun);
         if (rc) return rc;
         if (rerun.empty()) break;
+        if (attempt == 7) return fail(c, SR_ERR_CUDA, "speculative re-runs did not settle after 8 attempts (tile-list capacity)");
         for (size_t i : rerun) {
             SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
             rc = enqueue_view(c, p.jobs[i].m, p.prim, p.width, p.height, p.frame_height, p.y_org, p.jobs[i].color, p.jobs[i].depth, p.flags, st, c->status.p + i);
@@ -581,7 +772,19 @@ int sr_create(sr_ctx** out, int device) {
              cudaEventCreateWithFlags(&c->ev_clear[i], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreate(&c->ev_begin) == cudaSuccess && cudaEventCreate(&c->ev_end) == cudaSuccess;
     for (int i = 0; ok && i <= MAX_PROF; ++i) ok = cudaEventCreate(&c->prof_ev[i]) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&c->gather_stream, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&c->ev_gather_in, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < 4; ++i) ok = cudaEventCreateWithFlags(&c->ev_gather_done[i], cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < 2; ++i) ok = cudaEventCreateWithFlags(&c->ev_bounce[i], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaMallocHost((void**)&c->h_bad, sizeof(unsigned long long)) == cudaSuccess &&
+         cudaMalloc((void**)&c->d_bad, sizeof(unsigned long long)) == cudaSuccess;
     if (!ok) { sr_destroy(c); return SR_ERR_CUDA; }
+    {
+        int nthreads = 4;
+        if (const char* e = getenv("SR_FILL_THREADS")) nthreads = std::max(0, std::min(64, atoi(e)));
+        c->pool = new HostPool(nthreads);
+    }
+    if (const char* e = getenv("SR_EPOCH0")) c->epoch0 = (unsigned)strtoul(e, nullptr, 0);
     *out = c;
     return SR_OK;
 }
@@ -604,6 +807,15 @@ void sr_destroy(sr_ctx* c) {
     if (c->ev_end) cudaEventDestroy(c->ev_end);
     for (int i = 0; i <= MAX_PROF; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->h_status) cudaFreeHost(c->h_status);
+    delete c->pool;
+    if (c->comm && Nccl::get().ok) Nccl::get().CommDestroy(c->comm);
+    c->mesh_stage.release();
+    for (int i = 0; i < 2; ++i) { if (c->bounce[i]) cudaFreeHost(c->bounce[i]); if (c->ev_bounce[i]) cudaEventDestroy(c->ev_bounce[i]); }
+    for (int i = 0; i < 4; ++i) if (c->ev_gather_done[i]) cudaEventDestroy(c->ev_gather_done[i]);
+    if (c->ev_gather_in) cudaEventDestroy(c->ev_gather_in);
+    if (c->h_bad) cudaFreeHost(c->h_bad);
+    if (c->d_bad) cudaFree(c->d_bad);
+    if (c->gather_stream) { cudaStreamSynchronize(c->gather_stream); cudaStreamDestroy(c->gather_stream); }
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     delete c;
@@ -618,45 +830,166 @@ int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64
     SR_CUDA(c, cudaSetDevice(c->device));
     if (c->pending.active) { int prc = sr_sync(c); if (prc == SR_ERR_CUDA) return prc; }
     SR_CUDA(c, cudaStreamSynchronize(c->stream));
+    const bool same_shape = c->has_mesh && nverts == c->nverts && nidx == c->nidx;
     c->has_mesh = false;
     SR_CUDA(c, c->pos.reserve(std::max<size_t>(3 * nverts, 1)));
     SR_CUDA(c, c->col.reserve(std::max<size_t>(nverts, 1)));
     SR_CUDA(c, c->idx.reserve(std::max<size_t>(nidx, 1)));
-    // stage the Swift-layout arrays, convert on the device
-    void* stage = nullptr;
+    // The Swift-layout arrays (32-B vertices R:154-157, Int indices R:196) go into one persistent staging buffer and are
+    // converted on the device.  Both copies and both conversions are enqueued back to back; the only host wait is the
+    // one for the index check.  (The reference hands the arrays over on every call, A:163: sr_render_pass runs this
+    // per frame, so nothing here allocates in the steady state.)
     const size_t vbytes = nverts * sizeof(sr_vertex), ibytes = nidx * sizeof(int64_t);
-    unsigned long long* d_bad = nullptr;
-    SR_CUDA(c, cudaMalloc(&stage, std::max<size_t>(std::max(vbytes, ibytes), 16)));
-    cudaError_t e = cudaMalloc((void**)&d_bad, sizeof(unsigned long long));
-    if (e != cudaSuccess) { cudaFree(stage); SR_CUDA(c, e); }
-    int rc = SR_OK;
-    do {
-        c->first_bad = ~0ull;
-        if ((e = cudaMemcpyAsync(d_bad, &c->first_bad, sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
-        if (nverts) {
-            if ((e = cudaMemcpyAsync(stage, vertices, vbytes, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
-            k_convert_vertices<<<div_up(nverts, 256), 256, 0, c->stream>>>((const float4*)stage, nverts, c->pos.p, c->col.p);
-        }
-        if (nidx) {
-            if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) break;   // stage is reused
-            if ((e = cudaMemcpyAsync(stage, indices, ibytes, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
-            k_convert_indices<<<div_up(nidx, 256), 256, 0, c->stream>>>((const long long*)stage, nidx, nverts, c->idx.p, d_bad);
-        }
-        if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpyAsync(&c->first_bad, d_bad, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) break;
-        e = cudaStreamSynchronize(c->stream);
-    } while (0);
-    cudaFree(stage);
-    cudaFree(d_bad);
-    SR_CUDA(c, e);
+    const size_t voff = 0, ioff = (vbytes + 255) & ~(size_t)255;
+    SR_CUDA(c, c->mesh_stage.reserve(std::max<size_t>(ioff + ibytes, 16)));
+    *c->h_bad = ~0ull;
+    SR_CUDA(c, cudaMemcpyAsync(c->d_bad, c->h_bad, sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+    if (nverts) {
+        int rc = upload(c, c->mesh_stage.p + voff, vertices, vbytes, c->stream);
+        if (rc) return rc;
+        k_convert_vertices<<<div_up(nverts, 256), 256, 0, c->stream>>>((const float4*)(c->mesh_stage.p + voff), nverts, c->pos.p, c->col.p);
+    }
+    if (nidx) {
+        int rc = upload(c, c->mesh_stage.p + ioff, indices, ibytes, c->stream);
+        if (rc) return rc;
+        k_convert_indices<<<div_up(nidx, 256), 256, 0, c->stream>>>((const long long*)(c->mesh_stage.p + ioff), nidx, nverts, c->idx.p, c->d_bad);
+    }
+    SR_CUDA(c, cudaGetLastError());
+    SR_CUDA(c, cudaMemcpyAsync(c->h_bad, c->d_bad, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    SR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->first_bad = *c->h_bad;
     c->nverts = nverts;
     c->nidx = nidx;
     c->has_mesh = true;
-    c->batched_mode = c->force_batches > 0;      // the adaptive policy starts over with every mesh
-    c->single_batch_pairs = 0;
-    c->nobin_mode = false;
-    c->z_lo = 0.0f; c->z_hi = 1.0f;
-    return rc;
+    c->mesh_generation++;
+    if (!same_shape) {
+        // the adaptive launch policies start over with a mesh of another size; a re-upload of the same shape (an
+        // animated mesh, or the strict per-call hand-over of sr_render_pass) keeps them: they are hints that every frame
+        // re-checks, results do not depend on them
+        c->batched_mode = c->force_batches > 0;
+        c->single_batch_pairs = 0;
+        c->nobin_mode = false;
+        c->z_lo = 0.0f; c->z_hi = 1.0f;
+    }
+    return SR_OK;
+}
+
+uint64_t sr_mesh_generation(const sr_ctx* c) { return c ? c->mesh_generation : 0; }
+
+int sr_host_alloc(sr_ctx* c, size_t bytes, void** out) {
+    if (!c || !out || bytes == 0) return SR_ERR_ARG;
+    *out = nullptr;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    SR_CUDA(c, cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+    return SR_OK;
+}
+
+int sr_host_free(sr_ctx* c, void* ptr) {
+    if (!c) return SR_ERR_ARG;
+    if (!ptr) return SR_OK;
+    SR_CUDA(c, cudaFreeHost(ptr));
+    return SR_OK;
+}
+
+int sr_host_register(sr_ctx* c, void* ptr, size_t bytes) {
+    if (!c || !ptr || bytes == 0) return SR_ERR_ARG;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    SR_CUDA(c, cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return SR_OK;
+}
+
+int sr_host_unregister(sr_ctx* c, void* ptr) {
+    if (!c || !ptr) return SR_ERR_ARG;
+    SR_CUDA(c, cudaHostUnregister(ptr));
+    return SR_OK;
+}
+
+// ---- composite gather over NCCL -------------------------------------------------------------------------------
+int sr_comm_unique_id(void* id128_out) {
+    if (!id128_out) return SR_ERR_ARG;
+    Nccl& n = Nccl::get();
+    if (!n.ok) return SR_ERR_COMM;
+    Nccl::UniqueId id;
+    if (n.GetUniqueId(&id) != 0) return SR_ERR_COMM;
+    std::memcpy(id128_out, &id, sizeof id);
+    return SR_OK;
+}
+
+int sr_comm_init(sr_ctx* c, const void* id128, int rank, int world) {
+    if (!c || !id128 || world <= 0 || rank < 0 || rank >= world) return SR_ERR_ARG;
+    Nccl& n = Nccl::get();
+    if (!n.ok) return fail(c, SR_ERR_COMM, n.why.c_str());
+    SR_CUDA(c, cudaSetDevice(c->device));
+    if (c->comm) { n.CommDestroy(c->comm); c->comm = nullptr; }
+    Nccl::UniqueId id;
+    std::memcpy(&id, id128, sizeof id);
+    const int rc = n.CommInitRank(&c->comm, world, id, rank);
+    if (rc != 0) { c->comm = nullptr; c->err = std::string("ncclCommInitRank: ") + n.GetErrorString(rc); return SR_ERR_COMM; }
+    c->comm_rank = rank;
+    c->comm_world = world;
+    return SR_OK;
+}
+
+int sr_comm_destroy(sr_ctx* c) {
+    if (!c) return SR_ERR_ARG;
+    if (c->comm) {
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->gather_stream);
+        Nccl::get().CommDestroy(c->comm);
+        c->comm = nullptr;
+    }
+    c->comm_rank = -1; c->comm_world = 0;
+    return SR_OK;
+}
+
+int sr_gather(sr_ctx* c, const void* send_dev, void* recv_dev, const size_t* bytes_per_rank, int root, int slot, void* after_stream) {
+    if (!c || !bytes_per_rank || slot < 0 || slot > 3) return SR_ERR_ARG;
+    if (!c->comm) return fail(c, SR_ERR_COMM, "sr_gather before sr_comm_init");
+    if (root < 0 || root >= c->comm_world) return fail(c, SR_ERR_ARG, "sr_gather: bad root");
+    const size_t mine = bytes_per_rank[c->comm_rank];
+    if ((mine && !send_dev) || (c->comm_rank == root && !recv_dev)) return fail(c, SR_ERR_ARG, "sr_gather: null buffer");
+    Nccl& n = Nccl::get();
+    SR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t after = after_stream ? (cudaStream_t)after_stream : c->stream;
+    SR_CUDA(c, cudaEventRecord(c->ev_gather_in, after));
+    SR_CUDA(c, cudaStreamWaitEvent(c->gather_stream, c->ev_gather_in, 0));
+    int rc = 0;
+    if (c->comm_rank == root) {
+        // the root's own block is a device copy; the others arrive as one grouped batch of receives
+        size_t off = 0;
+        for (int r = 0; r < root; ++r) off += bytes_per_rank[r];
+        if (mine && static_cast<char*>(recv_dev) + off != send_dev)
+            SR_CUDA(c, cudaMemcpyAsync(static_cast<char*>(recv_dev) + off, send_dev, mine, cudaMemcpyDeviceToDevice, c->gather_stream));
+        rc = n.GroupStart();
+        off = 0;
+        for (int r = 0; r < c->comm_world && rc == 0; ++r) {
+            if (r != root && bytes_per_rank[r]) rc = n.Recv(static_cast<char*>(recv_dev) + off, bytes_per_rank[r], kNcclUint8, r, c->comm, c->gather_stream);
+            off += bytes_per_rank[r];
+        }
+        const int rc2 = n.GroupEnd();
+        if (rc == 0) rc = rc2;
+    } else if (mine) {
+        rc = n.Send(send_dev, mine, kNcclUint8, root, c->comm, c->gather_stream);
+    }
+    if (rc != 0) { c->err = std::string("sr_gather: ") + n.GetErrorString(rc); return SR_ERR_COMM; }
+    SR_CUDA(c, cudaEventRecord(c->ev_gather_done[slot], c->gather_stream));
+    c->gather_slot_used[slot] = true;
+    return SR_OK;
+}
+
+int sr_gather_fence(sr_ctx* c, int slot, void* stream) {
+    if (!c || slot < 0 || slot > 3) return SR_ERR_ARG;
+    if (!c->gather_slot_used[slot]) return SR_OK;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    SR_CUDA(c, cudaStreamWaitEvent(stream ? (cudaStream_t)stream : c->stream, c->ev_gather_done[slot], 0));
+    return SR_OK;
+}
+
+int sr_gather_sync(sr_ctx* c) {
+    if (!c) return SR_ERR_ARG;
+    SR_CUDA(c, cudaSetDevice(c->device));
+    SR_CUDA(c, cudaStreamSynchronize(c->gather_stream));
+    return SR_OK;
 }
 
 int sr_render_device(sr_ctx* c, const float* transforms, size_t nviews, int prim, int W, int H, void* color_dev,
@@ -734,6 +1067,17 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
     const bool early_depth = want_depth && !((flags & SR_FLAG_DEPTH_LESS) && prim == SR_TRIANGLE);
     const uint32_t view_flags = early_depth ? (flags | SR_FLAG_NO_DEPTH_OUT) : flags;
     const size_t npx = (size_t)W * H;
+    // ... and a constant need not cross PCIe at all: the helper threads write +inf into the caller's image while the GPU
+    // renders (streaming stores), or - on the caller's word that the image still holds the plane the previous call left
+    // there (SR_FLAG_DEPTH_UNTOUCHED) - nothing is written.  SR_FILL_THREADS=0 keeps the PCIe copy.
+    const size_t depth_bytes = nviews * npx * sizeof(float);
+    const bool plane_kept = early_depth && (flags & SR_FLAG_DEPTH_UNTOUCHED) && c->last_depth_cleared &&
+                            c->last_depth_ptr == depth && c->last_depth_bytes == depth_bytes;
+    const bool host_fill = early_depth && !plane_kept && c->pool->threads() > 0;
+    const bool pcie_plane = early_depth && !plane_kept && !host_fill;
+    struct PoolWait { HostPool* p; ~PoolWait() { if (p) p->wait(); } } pool_wait{host_fill ? c->pool : nullptr};
+    if (want_depth) { c->last_depth_ptr = depth; c->last_depth_bytes = depth_bytes; c->last_depth_cleared = false; }
+    if (host_fill) c->pool->start(HostPool::FILL_INF, depth, nullptr, depth_bytes);
     rc = ensure_frame_buffers(c, W, H, (flags & SR_FLAG_DEPTH_LESS) != 0, nviews, st);
     if (rc) return rc;
     for (int b = 0; b < 2; ++b) {
@@ -746,7 +1090,7 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
     for (size_t i = 0; i < nviews; ++i) {
         const int b = (int)(i & 1);
         if (i >= 2) SR_CUDA(c, cudaStreamWaitEvent(st, c->ev_copy[b], 0));
-        if (early_depth) {      // the render stream clears (it runs ahead of the copies), the copy stream only copies
+        if (pcie_plane) {       // the render stream clears (it runs ahead of the copies), the copy stream only copies
             k_clear_depth<<<div_up(div_up(npx, 4), 256), 256, 0, st>>>(c->out_depth[b].p, npx);
             SR_CUDA(c, cudaGetLastError());
             c->launches++;
@@ -770,6 +1114,7 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
         rc = collect_status(c, nviews, st, &rerun);
         if (rc) return rc;
         if (rerun.empty()) break;
+        if (attempt == 7) return fail(c, SR_ERR_CUDA, "speculative re-runs did not settle after 8 attempts (tile-list capacity)");
         for (size_t i : rerun) {
             SR_CUDA(c, cudaMemsetAsync(c->status.p + i, 0, sizeof(ViewStatus), st));
             rc = enqueue_view(c, transforms + 16 * i, prim, W, H, Hframe, band.y0, c->out_color[0].p, (want_depth && !early_depth) ? c->out_depth[0].p : nullptr, view_flags, st, c->status.p + i);
@@ -785,6 +1130,7 @@ int sr_render_batch(sr_ctx* c, const float* transforms, size_t nviews, int prim,
     finish_profile(c);
     accumulate_stats(c, nviews, prim);
     c->stats.gpu_launches = c->launches;
+    if (want_depth) c->last_depth_cleared = early_depth;
     return c->stats.domain_skipped ? SR_ERR_DOMAIN : SR_OK;
 }
 

@@ -20,15 +20,18 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SR_LIB") or os.path.join(_HERE, "libsr_cuda.so")   # SR_LIB: a debug build (e.g. -DSR_TIMELINE)
 
-SR_OK, SR_ERR_ARG, SR_ERR_INDEX, SR_ERR_DOMAIN, SR_ERR_CUDA, SR_ERR_NOMESH = 0, -1, -2, -3, -4, -5
+SR_OK, SR_ERR_ARG, SR_ERR_INDEX, SR_ERR_DOMAIN, SR_ERR_CUDA, SR_ERR_NOMESH, SR_ERR_COMM = 0, -1, -2, -3, -4, -5, -6
 FLAG_DEPTH_LESS = 1 << 0
 FLAG_NO_DEPTH_OUT = 1 << 1
+FLAG_DEPTH_UNTOUCHED = 1 << 2
 
 #: every symbol include/sr_cuda.h declares
 ABI_SYMBOLS = (
     "sr_version", "sr_create", "sr_destroy", "sr_last_error", "sr_set_mesh", "sr_render", "sr_render_pass",
     "sr_render_batch", "sr_render_device", "sr_sync", "sr_get_stats", "sr_get_kernel_times", "sr_set_profiling",
-    "sr_draw2d", "sr_set_band",
+    "sr_draw2d", "sr_set_band", "sr_mesh_generation", "sr_host_alloc", "sr_host_free", "sr_host_register",
+    "sr_host_unregister", "sr_comm_unique_id", "sr_comm_init", "sr_comm_destroy", "sr_gather", "sr_gather_fence",
+    "sr_gather_sync",
 )
 
 
@@ -150,6 +153,28 @@ def load_library():
     L.sr_draw2d.argtypes = [vp, vp, sz, i32, i32, vp]
     L.sr_set_band.restype = i32
     L.sr_set_band.argtypes = [vp, i32, i32]
+    L.sr_mesh_generation.restype = ctypes.c_uint64
+    L.sr_mesh_generation.argtypes = [vp]
+    L.sr_host_alloc.restype = i32
+    L.sr_host_alloc.argtypes = [vp, sz, ctypes.POINTER(vp)]
+    L.sr_host_free.restype = i32
+    L.sr_host_free.argtypes = [vp, vp]
+    L.sr_host_register.restype = i32
+    L.sr_host_register.argtypes = [vp, vp, sz]
+    L.sr_host_unregister.restype = i32
+    L.sr_host_unregister.argtypes = [vp, vp]
+    L.sr_comm_unique_id.restype = i32
+    L.sr_comm_unique_id.argtypes = [vp]
+    L.sr_comm_init.restype = i32
+    L.sr_comm_init.argtypes = [vp, vp, i32, i32]
+    L.sr_comm_destroy.restype = i32
+    L.sr_comm_destroy.argtypes = [vp]
+    L.sr_gather.restype = i32
+    L.sr_gather.argtypes = [vp, vp, vp, ctypes.POINTER(sz), i32, i32, vp]
+    L.sr_gather_fence.restype = i32
+    L.sr_gather_fence.argtypes = [vp, i32, vp]
+    L.sr_gather_sync.restype = i32
+    L.sr_gather_sync.argtypes = [vp]
     _lib = L
     return L
 
@@ -180,6 +205,10 @@ class RenderPass:
     indices: np.ndarray
     primitive_type: PrimitiveType = PrimitiveType.triangle
     transform: np.ndarray = field(default_factory=lambda: np.eye(4, dtype=np.float32))
+    #: None (default) = the reference's contract: the arrays are handed over and uploaded on EVERY call (App.swift:163).
+    #: An integer = "static mesh" opt-in: the arrays are uploaded when this number (or the array sizes) differs from the
+    #: one uploaded last; the caller bumps it after editing vertices / indices.  Not a field of the reference's RenderPass.
+    mesh_version: int | None = None
 
 
 def _colmajor(transform) -> np.ndarray:
@@ -201,12 +230,17 @@ class CudaRenderer:
             raise SrError(rc, "sr_create failed: no CUDA device / CUDA runtime error (there is no CPU fallback)")
         self.device = device
         self.depth_test = False      # True = run the depth test of Renderer.swift:257-261
-        self._mesh_key = None
+        self.depth_untouched = False  # True = host calls pass SR_FLAG_DEPTH_UNTOUCHED (see include/sr_cuda.h)
+        self._mesh_key = None        # (mesh_version, nverts, nidx, library generation) of the static-mesh opt-in
         self._band = None            # (y0, y1): render only these rows of each frame (set_band)
+        self._host_blocks = {}       # address -> keep-alive of arrays handed out by host_array()
 
     # -- lifetime ----------------------------------------------------------------------------------------------
     def close(self):
         if getattr(self, "_ctx", None) and self._ctx.value:
+            for addr in list(getattr(self, "_host_blocks", {})):
+                self._lib.sr_host_free(self._ctx, ctypes.c_void_p(addr))
+            self._host_blocks = {}
             self._lib.sr_destroy(self._ctx)
             self._ctx = ctypes.c_void_p()
 
@@ -231,15 +265,41 @@ class CudaRenderer:
             raise DomainError(rc, f"{self.stats()['domain_skipped']} primitive(s) skipped by the domain rule")
         raise SrError(rc, msg)
 
-    def _flags(self, want_depth: bool) -> int:
-        return (FLAG_DEPTH_LESS if self.depth_test else 0) | (0 if want_depth else FLAG_NO_DEPTH_OUT)
+    def _flags(self, want_depth: bool, host: bool = False) -> int:
+        return ((FLAG_DEPTH_LESS if self.depth_test else 0) | (0 if want_depth else FLAG_NO_DEPTH_OUT) |
+                (FLAG_DEPTH_UNTOUCHED if (host and self.depth_untouched) else 0))
+
+    # -- page-locked host memory (sr_host_alloc) ---------------------------------------------------------------
+    def host_array(self, shape, dtype) -> np.ndarray:
+        """A numpy array in page-locked memory from sr_host_alloc (freed by close()): images and mesh arrays kept here
+        are read / written by the GPU's copy engines directly."""
+        dt = np.dtype(dtype)
+        n = int(np.prod(shape)) * dt.itemsize
+        p = ctypes.c_void_p()
+        self._check(self._lib.sr_host_alloc(self._ctx, max(n, 1), ctypes.byref(p)))
+        buf = (ctypes.c_uint8 * max(n, 1)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+        self._host_blocks[p.value] = buf
+        return arr
+
+    def host_register(self, array: np.ndarray):
+        """Page-locks memory the caller already owns (sr_host_register); undo with host_unregister."""
+        self._check(self._lib.sr_host_register(self._ctx, array.ctypes.data, array.nbytes))
+
+    def host_unregister(self, array: np.ndarray):
+        self._check(self._lib.sr_host_unregister(self._ctx, array.ctypes.data))
 
     # -- mesh --------------------------------------------------------------------------------------------------
-    def set_mesh(self, vertices: np.ndarray, indices: np.ndarray):
+    @staticmethod
+    def _mesh_arrays(vertices, indices):
         v = np.ascontiguousarray(vertices, dtype=np.float32)
         if v.ndim != 2 or v.shape[1] != 8:
             raise ValueError("vertices must be (N, 8) float32 rows: x y z _ r g b _")
-        idx = np.ascontiguousarray(indices, dtype=np.int64).reshape(-1)
+        return v, np.ascontiguousarray(indices, dtype=np.int64).reshape(-1)
+
+    def set_mesh(self, vertices: np.ndarray, indices: np.ndarray):
+        """Explicit upload (sr_set_mesh) for render_views / render_device and for passes with a `mesh_version`."""
+        v, idx = self._mesh_arrays(vertices, indices)
         self._check(self._lib.sr_set_mesh(self._ctx, v.ctypes.data, v.shape[0], idx.ctypes.data, idx.shape[0]))
         self._mesh_key = None
 
@@ -257,13 +317,10 @@ class CudaRenderer:
     def render(self, render_pass: RenderPass):
         """Renderer.render(renderPass:) (Renderer.swift:204-230): synchronous, writes both images in place
         (with a band set: rows [y0, y1) of both images, the rest is left untouched).
-        The mesh arrays travel with the pass, as in the reference (App.swift:163); they are re-uploaded only when
-        the array OBJECTS handed over are not the ones uploaded last; after modifying them in place call set_mesh."""
+        The mesh arrays travel with the pass and are uploaded on every call, as the reference hands them over
+        (App.swift:163; sr_render_pass) - unless the pass opts into a static mesh with `mesh_version` (then they are
+        uploaded when the version or the array sizes change; there is no guessing from addresses or object identity)."""
         rp = render_pass
-        key = self._mesh_key
-        if key is None or key[0] is not rp.vertices or key[1] is not rp.indices:
-            self.set_mesh(rp.vertices, rp.indices)
-            self._mesh_key = (rp.vertices, rp.indices)     # strong refs: identity cannot be recycled
         col, dep = rp.color_buffer.array, rp.depth_buffer.array
         W, H = rp.color_buffer.width, rp.color_buffer.height
         assert col.dtype == np.uint8 and col.flags.c_contiguous and col.size == W * H * 4
@@ -271,8 +328,18 @@ class CudaRenderer:
         m = _colmajor(rp.transform)
         # with a band set only rows [y0, y1) of the pass's images are written: packed rows, so the band is one block
         y0 = 0 if self._band is None else self._band[0]
-        self._check(self._lib.sr_render(self._ctx, m.ctypes.data, int(rp.primitive_type), W, H,
-                                        col.ctypes.data + 4 * W * y0, dep.ctypes.data + 4 * W * y0, self._flags(True)))
+        cptr, dptr = col.ctypes.data + 4 * W * y0, dep.ctypes.data + 4 * W * y0
+        if rp.mesh_version is None:
+            v, idx = self._mesh_arrays(rp.vertices, rp.indices)
+            self._mesh_key = None
+            self._check(self._lib.sr_render_pass(self._ctx, v.ctypes.data, v.shape[0], idx.ctypes.data, idx.shape[0],
+                                                 m.ctypes.data, int(rp.primitive_type), W, H, cptr, dptr, self._flags(True, True)))
+            return
+        key = (int(rp.mesh_version), int(np.shape(rp.vertices)[0]), int(np.size(rp.indices)))
+        if self._mesh_key is None or self._mesh_key[:3] != key or self._mesh_key[3] != self._lib.sr_mesh_generation(self._ctx):
+            self.set_mesh(rp.vertices, rp.indices)
+            self._mesh_key = key + (self._lib.sr_mesh_generation(self._ctx),)
+        self._check(self._lib.sr_render(self._ctx, m.ctypes.data, int(rp.primitive_type), W, H, cptr, dptr, self._flags(True, True)))
 
     def render_views(self, transforms, width: int, height: int, primitive_type=PrimitiveType.triangle,
                      color_out: np.ndarray | None = None, depth_out: np.ndarray | None = None, want_depth=True):
@@ -288,7 +355,7 @@ class CudaRenderer:
         assert color.size >= n * rows * width * 4 and (depth is None or depth.size >= n * rows * width)
         rc = self._lib.sr_render_batch(self._ctx, m.ctypes.data, n, int(primitive_type), width, height,
                                        color.ctypes.data, depth.ctypes.data if depth is not None else None,
-                                       self._flags(want_depth))
+                                       self._flags(want_depth, True))
         self._check(rc)
         return color, depth
 

@@ -9,7 +9,12 @@ let package = Package(
     targets: [
         // C module map over include/sr_cuda.h; links libsr_cuda.so (software_renderer_b200/libsr_cuda.so)
         .systemLibrary(name: "CSRCuda", path: "Sources/CSRCuda"),
-        .target(name: "SoftwareRendererCUDA", dependencies: ["CSRCuda"],
+        // Linux stand-ins for Apple's `simd` and `Metal` modules (types + the three closed simd operations, DESIGN.md §2)
+        .target(name: "simd", path: "Sources/simd"),
+        .target(name: "Metal", path: "Sources/Metal"),
+        // the reference's Renderer.swift, unchanged, as a second oracle: link the file in first (Sources/ReferenceOracle/README.md)
+        .target(name: "ReferenceOracle", dependencies: ["simd", "Metal"], path: "Sources/ReferenceOracle", exclude: ["README.md"]),
+        .target(name: "SoftwareRendererCUDA", dependencies: ["CSRCuda", "simd"],
                 linkerSettings: [.unsafeFlags(["-L../software_renderer_b200", "-Xlinker", "-rpath", "-Xlinker", "../software_renderer_b200"])]),
     ]
 )

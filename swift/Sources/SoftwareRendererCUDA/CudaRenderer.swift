@@ -4,6 +4,7 @@
 // UNVERIFIED: this file cannot be compiled in this repository's image (no Swift toolchain).  The C ABI it binds is
 // exercised by tests/ through ctypes.
 import CSRCuda
+import simd          // Apple's module on Darwin, Sources/simd on Linux
 
 public typealias ColorImage = Image<Pixel>
 public typealias DepthImage = Image<Float>
@@ -41,6 +42,10 @@ public struct RenderPass {
     public var indices: [Int]
     public var primitiveType: PrimitiveType = .triangle
     public var transform: matrix_float4x4 = .init(diagonal: .init(1, 1, 1, 1))
+    /// nil (default) = the reference's contract: the arrays are handed over and uploaded on EVERY call (App.swift:163).
+    /// A number = "static mesh" opt-in: uploaded when it (or an array count) differs from the upload before; the caller
+    /// bumps it after editing `vertices` / `indices`.  Not a field of the reference's RenderPass.
+    public var meshVersion: Int? = nil
     public init(colorBuffer: ColorImage, depthBuffer: DepthImage, vertices: [Vertex], indices: [Int]) {
         self.colorBuffer = colorBuffer; self.depthBuffer = depthBuffer; self.vertices = vertices; self.indices = indices
     }
@@ -61,9 +66,10 @@ public final class CudaRenderer {
     public var depthTest = false
     /// Set when the last pass skipped primitives outside the valid domain (the reference would have trapped).
     public private(set) var lastDomainSkips: UInt64 = 0
-    // the arrays of the previous pass: re-upload only when they change (GpuRenderer caches by length, G:41-67)
-    private var meshCount: (Int, Int) = (-1, -1)
-    private var meshHash: Int = 0
+    /// true = pass SR_FLAG_DEPTH_UNTOUCHED: the depth image still holds what the previous call left there
+    public var depthUntouched = false
+    // static-mesh opt-in (RenderPass.meshVersion): what was uploaded last
+    private var meshKey: (version: Int, nverts: Int, nidx: Int, generation: UInt64)? = nil
 
     public init(device: Int32 = 0) throws {
         precondition(MemoryLayout<Vertex>.stride == 32 && MemoryLayout<Int>.size == 8)
@@ -85,33 +91,61 @@ public final class CudaRenderer {
     /// colorBuffer and depthBuffer in place.
     public func render(renderPass: RenderPass) {
         let w = Int32(renderPass.colorBuffer.width), h = Int32(renderPass.colorBuffer.height)
-        var hasher = Hasher()
-        renderPass.vertices.withUnsafeBytes { hasher.combine(bytes: $0) }
-        renderPass.indices.withUnsafeBytes { hasher.combine(bytes: $0) }
-        let hash = hasher.finalize()
-        if meshCount != (renderPass.vertices.count, renderPass.indices.count) || hash != meshHash {
-            let rc = renderPass.vertices.withUnsafeBytes { vb in
+        var m = renderPass.transform
+        let flags: UInt32 = (depthTest ? UInt32(SR_FLAG_DEPTH_LESS) : 0) | (depthUntouched ? UInt32(SR_FLAG_DEPTH_UNTOUCHED) : 0)
+        let skip = bandStart * renderPass.colorBuffer.width          // packed rows: a band is one block of the image
+        let color = UnsafeMutableRawPointer(renderPass.colorBuffer.pointer + skip).assumingMemoryBound(to: UInt8.self)
+        let depth = renderPass.depthBuffer.pointer + skip
+        var rc: Int32 = 0
+        if let version = renderPass.meshVersion {
+            // static mesh: upload on a version / size change only (no hashing, no guessing from addresses)
+            let key = (version, renderPass.vertices.count, renderPass.indices.count, sr_mesh_generation(ctx))
+            if meshKey == nil || meshKey! != key {
+                setMesh(vertices: renderPass.vertices, indices: renderPass.indices)
+                meshKey = (version, renderPass.vertices.count, renderPass.indices.count, sr_mesh_generation(ctx))
+            }
+            rc = withUnsafeBytes(of: &m) { mb in
+                sr_render(ctx, mb.baseAddress!.assumingMemoryBound(to: Float.self), renderPass.primitiveType.raw, w, h, color, depth, flags)
+            }
+        } else {
+            // the reference's contract: vertices and indices travel with every call (App.swift:163) -> sr_render_pass
+            meshKey = nil
+            rc = renderPass.vertices.withUnsafeBytes { vb in
                 renderPass.indices.withUnsafeBufferPointer { ib in
-                    sr_set_mesh(ctx, vb.baseAddress?.assumingMemoryBound(to: sr_vertex.self), renderPass.vertices.count,
-                                UnsafeRawPointer(ib.baseAddress)?.assumingMemoryBound(to: Int64.self), renderPass.indices.count)
+                    withUnsafeBytes(of: &m) { mb in
+                        sr_render_pass(ctx, vb.baseAddress?.assumingMemoryBound(to: sr_vertex.self), renderPass.vertices.count,
+                                       UnsafeRawPointer(ib.baseAddress)?.assumingMemoryBound(to: Int64.self), renderPass.indices.count,
+                                       mb.baseAddress!.assumingMemoryBound(to: Float.self), renderPass.primitiveType.raw, w, h, color, depth, flags)
+                    }
                 }
             }
-            precondition(rc == 0, String(cString: sr_last_error(ctx)))   // Renderer.swift:226 traps on a bad index
-            meshCount = (renderPass.vertices.count, renderPass.indices.count); meshHash = hash
-        }
-        var m = renderPass.transform
-        let flags: UInt32 = depthTest ? UInt32(SR_FLAG_DEPTH_LESS) : 0
-        let skip = bandStart * renderPass.colorBuffer.width          // packed rows: a band is one block of the image
-        let rc = withUnsafeBytes(of: &m) { mb in
-            sr_render(ctx, mb.baseAddress!.assumingMemoryBound(to: Float.self), renderPass.primitiveType.raw, w, h,
-                      UnsafeMutableRawPointer(renderPass.colorBuffer.pointer + skip).assumingMemoryBound(to: UInt8.self),
-                      renderPass.depthBuffer.pointer + skip, flags)
         }
         var st = sr_stats()
         sr_get_stats(ctx, &st)
         lastDomainSkips = st.domain_skipped
-        precondition(rc == 0 || rc == SR_ERR_DOMAIN.rawValue, String(cString: sr_last_error(ctx)))
+        precondition(rc == 0 || rc == SR_ERR_DOMAIN.rawValue, String(cString: sr_last_error(ctx)))   // Renderer.swift:226 traps on a bad index
     }
+
+    /// Explicit upload (sr_set_mesh) for passes that carry a `meshVersion`.
+    public func setMesh(vertices: [Vertex], indices: [Int]) {
+        let rc = vertices.withUnsafeBytes { vb in
+            indices.withUnsafeBufferPointer { ib in
+                sr_set_mesh(ctx, vb.baseAddress?.assumingMemoryBound(to: sr_vertex.self), vertices.count,
+                            UnsafeRawPointer(ib.baseAddress)?.assumingMemoryBound(to: Int64.self), indices.count)
+            }
+        }
+        precondition(rc == 0, String(cString: sr_last_error(ctx)))
+        meshKey = nil
+    }
+
+    /// Page-locked memory for the colour / depth images (sr_host_alloc): the GPU's copy engines write it directly.
+    public func hostAlloc<T>(_ type: T.Type, count: Int) -> UnsafeMutablePointer<T> {
+        var p: UnsafeMutableRawPointer? = nil
+        let rc = sr_host_alloc(ctx, count * MemoryLayout<T>.stride, &p)
+        precondition(rc == 0 && p != nil, String(cString: sr_last_error(ctx)))
+        return p!.bindMemory(to: T.self, capacity: count)
+    }
+    public func hostFree<T>(_ p: UnsafeMutablePointer<T>) { _ = sr_host_free(ctx, UnsafeMutableRawPointer(p)) }
 
     // MARK: legacy 2-D immediate API (Renderer.swift:376-465) — same signatures, one sr_draw2d command each
 
