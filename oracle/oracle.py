@@ -14,6 +14,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libsr_oracle.so")
+_LIB_PATH_FMA = os.path.join(_HERE, "libsr_oracle_fma.so")     # -DSR_SIMD_FMA: Apple's simd_muladd fused (arm64)
 
 TRIANGLE, LINE, VERTICES = 0, 1, 2
 DEPTH_LESS = 1 << 0
@@ -37,21 +38,21 @@ class Stats(ctypes.Structure):
 def build(force: bool = False) -> str:
     """Compile the oracle with its own Makefile (g++ -O2 -ffp-contract=off)."""
     src = os.path.join(_HERE, "sr_oracle.cpp")
-    stale = (not os.path.exists(_LIB_PATH)) or os.path.getmtime(_LIB_PATH) < max(
-        os.path.getmtime(src), os.path.getmtime(os.path.join(_HERE, "sr_oracle.h")))
+    newest = max(os.path.getmtime(src), os.path.getmtime(os.path.join(_HERE, "sr_oracle.h")))
+    stale = any((not os.path.exists(q)) or os.path.getmtime(q) < newest for q in (_LIB_PATH, _LIB_PATH_FMA))
     if force or stale:
         subprocess.run(["make", "-C", _HERE, "clean", "all"], check=True, stdout=subprocess.DEVNULL)
     return _LIB_PATH
 
 
-_lib = None
+_libs = {}
 
 
-def lib():
-    global _lib
-    if _lib is None:
+def lib(simd_fma: bool = False):
+    """The oracle library: the default (every * and + rounded separately) or the SR_SIMD_FMA variant."""
+    if simd_fma not in _libs:
         build()
-        L = ctypes.CDLL(_LIB_PATH)
+        L = ctypes.CDLL(_LIB_PATH_FMA if simd_fma else _LIB_PATH)
         L.sr_oracle_render.restype = ctypes.c_int
         L.sr_oracle_render.argtypes = [
             ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int,
@@ -66,8 +67,8 @@ def lib():
         L.sr_oracle_pack_pixel.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.sr_oracle_draw2d.restype = ctypes.c_int
         L.sr_oracle_draw2d.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
-        _lib = L
-    return _lib
+        _libs[simd_fma] = L
+    return _libs[simd_fma]
 
 
 def _vertices32(vertices: np.ndarray) -> np.ndarray:
@@ -78,7 +79,7 @@ def _vertices32(vertices: np.ndarray) -> np.ndarray:
 
 
 def render(vertices, indices, transform, width, height, primitive_type=TRIANGLE, flags=0,
-           color_out=None, depth_out=None):
+           color_out=None, depth_out=None, simd_fma=False):
     """Returns (rc, color[H,W,4] uint8 BGRA, depth[H,W] float32, stats dict).
 
     `transform` is a (4,4) numpy matrix in the usual row-major maths sense (M @ v); it is handed to the
@@ -90,7 +91,7 @@ def render(vertices, indices, transform, width, height, primitive_type=TRIANGLE,
     color = color_out if color_out is not None else np.empty((height, width, 4), dtype=np.uint8)
     depth = depth_out if depth_out is not None else np.empty((height, width), dtype=np.float32)
     st = Stats()
-    rc = lib().sr_oracle_render(v.ctypes.data, v.shape[0], idx.ctypes.data, idx.shape[0], m.ctypes.data,
+    rc = lib(simd_fma).sr_oracle_render(v.ctypes.data, v.shape[0], idx.ctypes.data, idx.shape[0], m.ctypes.data,
                                 int(primitive_type), int(width), int(height), color.ctypes.data, depth.ctypes.data,
                                 int(flags), ctypes.byref(st))
     return rc, color, depth, st.as_dict()

@@ -18,13 +18,25 @@ struct ScreenVertex { F3 xyz; F3 color; };
 
 // ---- simd shim (the three defined operations; header comment items (1)-(3)) ------------------
 
-// simd_mul(float4x4, float4) for v = (x,y,z,1)  — R:160.  Column accumulate, unfused.
+// simd_muladd(a, b, c): Apple's simd_mul accumulates with it (r = c0*x; r = muladd(c1, y, r); ...).  On x86 without FMA it
+// is a*b + c rounded twice (the default here and in csrc/); on arm64 - the platform the reference ships on - the
+// compiler contracts it into one fused multiply-add.  -DSR_SIMD_FMA builds that variant (libsr_oracle_fma.so, mirrored
+// by libsr_cuda_fma.so), so the uncertainty of "bit-exact coverage" can be measured (tests/test_simd_fma.py).
+inline float muladd(float a, float b, float c) {
+#ifdef SR_SIMD_FMA
+    return fmaf(a, b, c);
+#else
+    return a * b + c;
+#endif
+}
+
+// simd_mul(float4x4, float4) for v = (x,y,z,1)  — R:160.  Column accumulate.
 inline void mat4_mul_point(const float* m, float x, float y, float z, float out[4]) {
     for (int r = 0; r < 4; ++r) {
         float acc = m[0 * 4 + r] * x;
-        acc = acc + m[1 * 4 + r] * y;
-        acc = acc + m[2 * 4 + r] * z;
-        acc = acc + m[3 * 4 + r] * 1.0f;
+        acc = muladd(m[1 * 4 + r], y, acc);
+        acc = muladd(m[2 * 4 + r], z, acc);
+        acc = muladd(m[3 * 4 + r], 1.0f, acc);
         out[r] = acc;
     }
 }
@@ -97,9 +109,9 @@ inline M2 triangle_T(L2 a, L2 b, L2 c) {
 
 inline F3 weights_from_T(const M2& t, float cfx, float cfy, float px, float py) {
     float dx = px - cfx, dy = py - cfy;
-    // simd_mul(float2x2, float2): c0*x then + c1*y, unfused  (R:91)
-    float wa = t.c0x * dx + t.c1x * dy;
-    float wb = t.c0y * dx + t.c1y * dy;
+    // simd_mul(float2x2, float2): c0*x, then muladd(c1, y, .)  (R:91)
+    float wa = muladd(t.c1x, dy, t.c0x * dx);
+    float wb = muladd(t.c1y, dy, t.c0y * dx);
     return F3{wa, wb, 1.0f - wa - wb};        // R:92
 }
 

@@ -12,6 +12,17 @@ namespace sr {
 
 struct Mat4 { float m[16]; };  // column-major, like matrix_float4x4 (R:199)
 
+// simd_muladd(a, b, c), the accumulation step of Apple's simd_mul (R:160, R:91): a*b + c rounded twice by default (x86
+// without FMA; "FMA contraction disabled"), one fused multiply-add with -DSR_SIMD_FMA (arm64, the platform the
+// reference ships on).  libsr_cuda_fma.so is the second build; oracle/ has the same switch.
+__device__ __forceinline__ float simd_muladd(float a, float b, float c) {
+#ifdef SR_SIMD_FMA
+    return __fmaf_rn(a, b, c);
+#else
+    return __fadd_rn(__fmul_rn(a, b), c);
+#endif
+}
+
 // Vertex.apply (R:159-163) + convertedToScreen (R:165-172).  Returns (sx, sy, z_ndc).
 // matrix * float4 is column accumulation with separately rounded * and + (the definition shared with oracle/).
 // WITH_Z = false leaves z_ndc out (returned as 0): with the depth test off nothing reads it.
@@ -22,9 +33,9 @@ __device__ __forceinline__ float3 transform_to_screen(const Mat4& M, float x, fl
     for (int r = 0; r < 4; ++r) {
         if (!WITH_Z && r == 2) { v[r] = 0.0f; continue; }
         float acc = __fmul_rn(M.m[r], x);
-        acc = __fadd_rn(acc, __fmul_rn(M.m[4 + r], y));
-        acc = __fadd_rn(acc, __fmul_rn(M.m[8 + r], z));
-        acc = __fadd_rn(acc, __fmul_rn(M.m[12 + r], 1.0f));
+        acc = simd_muladd(M.m[4 + r], y, acc);
+        acc = simd_muladd(M.m[8 + r], z, acc);
+        acc = simd_muladd(M.m[12 + r], 1.0f, acc);
         v[r] = acc;
     }
     float nx = __fdiv_rn(v[0], v[3]);   // R:161: three true divisions, no reciprocal
@@ -164,8 +175,8 @@ __device__ __forceinline__ BaryT bary_setup(int ax, int ay, int bx, int by, int 
 __device__ __forceinline__ float3 bary_weights(const BaryT& t, int x, int y) {
     float px = __fadd_rn(__int2float_rn(x), 0.5f), py = __fadd_rn(__int2float_rn(y), 0.5f);
     float dx = __fsub_rn(px, t.cfx), dy = __fsub_rn(py, t.cfy);
-    float wa = __fadd_rn(__fmul_rn(t.c0x, dx), __fmul_rn(t.c1x, dy));
-    float wb = __fadd_rn(__fmul_rn(t.c0y, dx), __fmul_rn(t.c1y, dy));
+    float wa = simd_muladd(t.c1x, dy, __fmul_rn(t.c0x, dx));     // simd_mul(float2x2, float2), R:91
+    float wb = simd_muladd(t.c1y, dy, __fmul_rn(t.c0y, dx));
     return make_float3(wa, wb, __fsub_rn(__fsub_rn(1.0f, wa), wb));
 }
 

@@ -45,6 +45,34 @@ def gather_framebuffers(local: torch.Tensor, nviews: int, dst: int = 0, group=No
     return None
 
 
+def init_comm(renderer, group=None) -> None:
+    """Joins `renderer`'s context to the job's NCCL communicator for sr_gather: rank 0 creates the NCCL id through the
+    C ABI (sr_comm_unique_id), torch.distributed carries the 128 bytes to the other ranks (any backend: this is host
+    plumbing), every rank calls sr_comm_init.  From here on the composite needs no torch on the data path."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    box = [type(renderer).comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    renderer.comm_init(box[0], rank, world)
+
+
+def view_block_bytes(nviews: int, world: int, bytes_per_view: int):
+    """bytes_per_rank argument of sr_gather for a block split of `nviews` views."""
+    return [(shard_range(nviews, r, world)[1] - shard_range(nviews, r, world)[0]) * bytes_per_view for r in range(world)]
+
+
+def gather_views(renderer, local: torch.Tensor, nviews: int, out: torch.Tensor | None, slot: int = 0, dst: int = 0,
+                 stream=None):
+    """sr_gather of this rank's finished framebuffers (n_local, H, W[, C]) into `out` (nviews, ...) on `dst`, in view
+    order, asynchronously on the context's gather stream (ordered after the rendering enqueued so far on `stream`).
+    Call renderer.gather_sync() (host) or renderer.gather_fence(slot) (device) before touching the buffers again."""
+    per_view = local[0].numel() * local.element_size() if local.shape[0] else (out[0].numel() * out.element_size())
+    sizes = view_block_bytes(nviews, renderer.comm_world, per_view)
+    assert local.is_contiguous() and (out is None or out.is_contiguous())
+    renderer.gather(local.data_ptr() if local.numel() else 0, out.data_ptr() if out is not None else None, sizes,
+                    root=dst, slot=slot, after_stream=stream)
+
+
 def band_range(height: int, rank: int, world: int, align: int = 16) -> Tuple[int, int]:
     """Rows [y0, y1) of ONE frame rendered by `rank` (screen-band split): the frame's tile
     rows (16 pixel rows each, the kernels' tile height) are block-split like views, so every band but the last is

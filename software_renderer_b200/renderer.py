@@ -19,6 +19,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SR_LIB") or os.path.join(_HERE, "libsr_cuda.so")   # SR_LIB: a debug build (e.g. -DSR_TIMELINE)
+#: the -DSR_SIMD_FMA build: Apple's simd_muladd fused, as arm64 compiles it; CudaRenderer(simd_fma=True)
+LIB_PATH_FMA = os.path.join(_HERE, "libsr_cuda_fma.so")
 
 SR_OK, SR_ERR_ARG, SR_ERR_INDEX, SR_ERR_DOMAIN, SR_ERR_CUDA, SR_ERR_NOMESH, SR_ERR_COMM = 0, -1, -2, -3, -4, -5, -6
 FLAG_DEPTH_LESS = 1 << 0
@@ -109,19 +111,19 @@ class DomainError(SrError):
     The frame was completed; the images hold everything else."""
 
 
-_lib = None
+_libs = {}
 
 
-def load_library():
-    """Loads libsr_cuda.so (built in-tree by __graft_entry__.build()).  Raises if it is missing."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
+def load_library(simd_fma: bool = False):
+    """Loads libsr_cuda.so (built in-tree by __graft_entry__.build()), or its SR_SIMD_FMA twin.  Raises if it is missing."""
+    path = LIB_PATH_FMA if simd_fma else LIB_PATH
+    if path in _libs:
+        return _libs[path]
+    if not os.path.exists(path):
         raise FileNotFoundError(
-            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(there is no CPU fallback)")
-    L = ctypes.CDLL(LIB_PATH)
+    L = ctypes.CDLL(path)
     vp, sz, i32, u32 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint32
     L.sr_version.restype = i32
     L.sr_version.argtypes = []
@@ -175,7 +177,7 @@ def load_library():
     L.sr_gather_fence.argtypes = [vp, i32, vp]
     L.sr_gather_sync.restype = i32
     L.sr_gather_sync.argtypes = [vp]
-    _lib = L
+    _libs[path] = L
     return L
 
 
@@ -221,8 +223,8 @@ def _colmajor(transform) -> np.ndarray:
 class CudaRenderer:
     """Drop-in for `Renderer` / `GpuRenderer` (App.swift:148-154) on one B200."""
 
-    def __init__(self, device: int = 0):
-        self._lib = load_library()
+    def __init__(self, device: int = 0, simd_fma: bool = False):
+        self._lib = load_library(simd_fma)
         self._ctx = ctypes.c_void_p()
         rc = self._lib.sr_create(ctypes.byref(self._ctx), int(device))
         if rc != SR_OK:
@@ -373,6 +375,39 @@ class CudaRenderer:
 
     def sync(self):
         self._check(self._lib.sr_sync(self._ctx))
+
+    # -- composite gather over NCCL (sr_gather) -----------------------------------------------
+    @staticmethod
+    def comm_unique_id(simd_fma: bool = False) -> bytes:
+        """The 128-byte NCCL id the root rank creates and hands to the others (sr_comm_unique_id)."""
+        buf = ctypes.create_string_buffer(128)
+        rc = load_library(simd_fma).sr_comm_unique_id(buf)
+        if rc != SR_OK:
+            raise SrError(rc, "sr_comm_unique_id failed: libnccl.so.2 could not be opened")
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, world: int):
+        assert len(unique_id) == 128
+        self._check(self._lib.sr_comm_init(self._ctx, ctypes.c_char_p(unique_id), int(rank), int(world)))
+        self.comm_rank, self.comm_world = int(rank), int(world)
+
+    def comm_destroy(self):
+        self._lib.sr_comm_destroy(self._ctx)
+
+    def gather(self, send_ptr: int, recv_ptr: int | None, bytes_per_rank, root: int = 0, slot: int = 0,
+               after_stream: int | None = None):
+        """Asynchronous gather of every rank's block to `root` (device pointers), ordered after the work this context
+        has enqueued on `after_stream` so far; runs on the context's gather stream."""
+        arr = (ctypes.c_size_t * len(bytes_per_rank))(*[int(b) for b in bytes_per_rank])
+        self._check(self._lib.sr_gather(self._ctx, ctypes.c_void_p(send_ptr) if send_ptr else None,
+                                        ctypes.c_void_p(recv_ptr) if recv_ptr else None, arr, int(root), int(slot),
+                                        ctypes.c_void_p(after_stream) if after_stream else None))
+
+    def gather_fence(self, slot: int, stream: int | None = None):
+        self._check(self._lib.sr_gather_fence(self._ctx, int(slot), ctypes.c_void_p(stream) if stream else None))
+
+    def gather_sync(self):
+        self._check(self._lib.sr_gather_sync(self._ctx))
 
     def draw2d(self, cmds, image: np.ndarray):
         """Runs legacy 2-D commands (Cmd2D.rect/circle/line/triangle) in order on a (H, W, 4) BGRA8 image, in place."""
