@@ -183,9 +183,8 @@ def run_reference(args):
         "impl": "reference", "metric": "frames_per_second", "value": value, "unit": "frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * t / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+i64", "data": "synthetic",
-        "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": int(v.shape[0]),
-                   "depth_test": bool(args.depth_test), "l2": "n/a (host cores)",
-                   "parallelism": f"{cores} host threads, one render pass each per step"},
+        "config": workload_config(desc, W, H, ntris, int(v.shape[0]), args.depth_test),
+        "run": {"l2": "n/a (host cores)", "parallelism": f"{cores} host threads, one render pass each per step"},
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -194,11 +193,351 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def workload_config(desc, W, H, ntris, nverts, depth_test):
+    """`config` of the JSON line: the workload and nothing else, identical in both arms (run-mode facts go to `run`)."""
+    return {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": nverts, "depth_test": bool(depth_test)}
+
+
+def device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, frame0, dev):
+    """K timed frames, device resident, L2 flushed between frames; returns (per-frame ms array, launches, wall s)."""
+    import torch
+
+    def frame(k):
+        r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream, sync=False)
+
+    with torch.cuda.stream(stream):
+        frame(0)
+        r.sync()                                        # lets the adaptive launch policies settle
+        for k in range(1, Wm):
+            frame(k)
+        r.sync()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for k in range(K):
+            if not os.environ.get("SR_BENCH_NOFLUSH"):
+                flush.fill_(k & 0xFF)                   # L2 flush between timed frames (not timed)
+            evs[k][0].record(stream)
+            frame(Wm + k)                               # asynchronous; calls accumulate, no host round trip
+            evs[k][1].record(stream)
+        r.sync()                                        # one status read-back for all K frames
+        launches = r.stats()["gpu_launches"]
+        torch.cuda.synchronize(dev)
+        wall = time.perf_counter() - t0
+    return np.array([a.elapsed_time(b) for a, b in evs]), int(launches), wall
+
+
+def kernel_split(r, xf, W, H, color, depth, stream, flush, frame0, dev, reps=5):
+    """Per-kernel device time of one frame (extra events between kernels; separate from the timed loop)."""
+    import torch
+    r.set_profiling(True)
+    acc = {}
+    with torch.cuda.stream(stream):
+        for k in range(reps):
+            flush.fill_(1)
+            torch.cuda.synchronize(dev)
+            r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream)
+            for nm, ms in r.kernel_times().items():
+                acc[nm] = acc.get(nm, 0.0) + ms / reps
+    r.set_profiling(False)
+    return acc
+
+
+def roofline_of(acc, ntris, nverts, W, H, workload_key):
+    """Roofline line of the dominant kernel.  Algorithmic bytes (12 B per triangle of indices, 24 B per
+    vertex of xyz + rgb, 8 B per pixel of colour + depth) are split over the kernels that touch them:
+    positions are read by k_transform, or - in batched frames, which do not launch it - by k_setup."""
+    hbm, peak_kind = peaks()
+    alg = {"k_transform": 12 * nverts, "k_setup": 12 * ntris + (0 if "k_transform" in acc else 12 * nverts),
+           "k_tile": 12 * nverts + 8 * W * H, "k_resolve": 12 * nverts + 8 * W * H}
+    top = max(acc, key=acc.get) if acc else "k_tile"
+    top_ms = acc.get(top, float("nan"))
+    top_bytes = alg.get(top, 0)
+    achieved = top_bytes / (top_ms * 1e-3) / 1e9 if top_ms and top_ms == top_ms else float("nan")
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get(workload_key, {}).get(top)
+        except Exception:
+            traffic = None
+    return {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+            "traffic": traffic, "algorithmic_bytes": top_bytes, "kernel_ms": top_ms, "peak_kind": peak_kind}
+
+
+def frame_roofline_of(frame_ms, ntris, nverts, W, H):
+    from software_renderer_b200 import scene as S
+    hbm, peak_kind = peaks()
+    b = S.algorithmic_bytes(ntris, nverts, W, H)
+    return {"bound": "hbm", "achieved": b / (frame_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+            "frac": b / (frame_ms * 1e-3) / 1e9 / hbm, "bytes_per_frame": b, "peak_kind": peak_kind}
+
+
+class E2E:
+    """End-to-end legs: the host-pointer C-ABI calls, host<->device copies inside the timed wall-clock region."""
+
+    def __init__(self, world, dev, K):
+        self.world, self.dev, self.K = world, dev, K
+
+    def timed(self, one_pass, frames_per_pass):
+        """`one_pass` is repeated until the wall-clock region is ~0.3 s (a 1080p frame takes 0.2 ms: K frames alone would be
+        a region of a few ms, at the mercy of one scheduler hiccup on one of N ranks).  Whole-job frames/s, max over ranks."""
+        import torch.distributed as dist
+        from software_renderer_b200.multi_gpu import max_over_ranks
+        t0 = time.perf_counter()
+        one_pass()
+        passes = int(min(200, max(1, np.ceil(0.3 / max(time.perf_counter() - t0, 1e-4)))))
+        passes = int(max_over_ranks(float(passes), device=self.dev))          # the same count on every rank
+        if self.world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(passes):
+            one_pass()
+        t = max_over_ranks(time.perf_counter() - t0, device=self.dev)
+        return self.world * frames_per_pass * passes / t, frames_per_pass * passes
+
+
+def e2e_suite(r, local, world, dev, v, i, xf, W, H, K, Wm, frame0, full: bool):
+    """Returns the `e2e` object.  Headline (`value`): sr_render_batch, 16 frames per call, page-locked caller images, mesh
+    uploaded once.  `full` (rank 0's N = 1 run) adds the variants a drop-in caller can meet: pageable images, the strict
+    per-call mesh hand-over of the reference (App.swift:163), and the three ways to treat the constant depth plane."""
+    import torch
+    import software_renderer_b200 as srb
+    e = E2E(world, dev, K)
+    CH = 16
+    mats = np.stack([xf(frame0 + Wm + k) for k in range(K)])
+
+    def batch_leg(rr, bc, bd):
+        rr.render_views(mats[:min(K, CH)], W, H, color_out=bc, depth_out=bd, want_depth=bd is not None)      # warm-up
+
+        def one():
+            for s0 in range(0, K, CH):
+                n = min(CH, K - s0)
+                rr.render_views(mats[s0:s0 + n], W, H, color_out=bc[:n], depth_out=None if bd is None else bd[:n], want_depth=bd is not None)
+        return e.timed(one, K)
+
+    bc = r.host_array((CH, H, W, 4), np.uint8)          # sr_host_alloc: page-locked
+    bd = r.host_array((CH, H, W), np.float32)
+    value, frames = batch_leg(r, bc, bd)
+    depth_mode = r.depth_test
+    out = {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 64,
+           "d2h_bytes_per_step": (8 if depth_mode else 4) * W * H,
+           "api": "sr_render_batch, 16 frames per call, page-locked host images (sr_host_alloc), mesh uploaded once by sr_set_mesh; "
+                  + ("colour and depth cross PCIe" if depth_mode else
+                     "colour crosses PCIe, the constant +inf depth plane (depth test off, Renderer.swift:206) is written into the caller's image by the library's host threads"),
+           "frames_timed_per_rank": frames}
+    # the same call with the depth plane left alone on the caller's word / not asked for at all
+    if not depth_mode:
+        r.depth_untouched = True
+        out["depth_untouched"] = {"value": batch_leg(r, bc, bd)[0], "unit": "frames/s", "api": "same, SR_FLAG_DEPTH_UNTOUCHED: the caller's depth image still holds the plane of the previous call"}
+        r.depth_untouched = False
+    out["no_depth_out"] = {"value": batch_leg(r, bc, None)[0], "unit": "frames/s", "api": "same, SR_FLAG_NO_DEPTH_OUT (colour only)"}
+    # bare copies of the same bytes on every rank at once: what this box can deliver (the e2e roofline)
+    out["pcie_probe"] = pcie_probe(e, local, dev, W, H, bc, bd)
+    if not full:
+        return out
+    if not depth_mode:
+        os.environ["SR_FILL_THREADS"] = "0"
+        with srb.CudaRenderer(local) as r0:
+            r0.set_mesh(v, i)
+            out["depth_over_pcie"] = {"value": batch_leg(r0, bc, bd)[0], "unit": "frames/s", "d2h_bytes_per_step": 8 * W * H,
+                                      "api": "same, SR_FILL_THREADS=0: the +inf plane is produced on the device and copied (round-1 behaviour)"}
+        del os.environ["SR_FILL_THREADS"]
+    pc, pd = np.empty((CH, H, W, 4), np.uint8), np.empty((CH, H, W), np.float32)
+    out["pageable_images"] = {"value": batch_leg(r, pc, pd)[0], "unit": "frames/s", "api": "same call, ordinary (pageable) caller images, as App.swift:59-60 allocates them"}
+    # one synchronous call per frame, static mesh (RenderPass.mesh_version)
+    rp = srb.RenderPass(srb.Image(bc[0], W, H), srb.Image(bd[0], W, H), v, i, srb.PrimitiveType.triangle, None, mesh_version=1)
+
+    def sync_pass():
+        for k in range(K):
+            rp.transform = mats[k]
+            r.render(rp)
+    sync_pass()
+    out["sync_per_frame"] = {"value": e.timed(sync_pass, K)[0], "unit": "frames/s", "api": "sr_render, one synchronous call per frame, page-locked images, static mesh (mesh_version)"}
+    # the reference's own contract: vertices and indices travel with EVERY call (App.swift:163) -> sr_render_pass
+    KS = max(4, min(K, 16))
+    mesh_bytes = int(v.nbytes + np.asarray(i, np.int64).nbytes)
+    pv = r.host_array(v.shape, np.float32)
+    pi = r.host_array((i.size,), np.int64)
+    pv[:] = v
+    pi[:] = i
+    strict = {}
+    for name, (vv, ii, cc, dd) in {"page_locked": (pv, pi, bc[0], bd[0]), "pageable": (v, np.ascontiguousarray(i, np.int64), pc[0], pd[0])}.items():
+        rps = srb.RenderPass(srb.Image(cc, W, H), srb.Image(dd, W, H), vv, ii, srb.PrimitiveType.triangle, None)
+
+        def strict_pass():
+            for k in range(KS):
+                rps.transform = mats[k % K]
+                r.render(rps)
+        strict_pass()
+        strict[name] = e.timed(strict_pass, KS)[0]
+    out["strict_render_pass"] = {"value": strict["pageable"], "unit": "frames/s", "page_locked_arrays": strict["page_locked"],
+                                 "h2d_bytes_per_step": mesh_bytes + 64,
+                                 "api": "sr_render_pass: mesh arrays (Swift layout: 32-B vertices, Int indices) re-sent on every call, as the reference hands them over; "
+                                        "value = ordinary caller memory for arrays and images, page_locked_arrays = both from sr_host_alloc"}
+    r.set_mesh(v, i)
+    return out
+
+
+def pcie_probe(e, local, dev, W, H, bc, bd):
+    """Bare cudaMemcpyAsync D2H of one frame's colour plane (and colour + depth) into the same page-locked images, all ranks at
+    once: GB/s per GPU and the frames/s that bandwidth allows.  No kernel of this repo runs."""
+    import torch
+    src = torch.empty(8 * W * H, dtype=torch.uint8, device=dev)
+    dst_c = torch.from_numpy(bc.reshape(-1))
+    dst_d = torch.from_numpy(bd.reshape(-1).view(np.uint8))
+    st = torch.cuda.Stream(device=dev)
+    res = {}
+    for name, planes in (("colour", 1), ("colour_and_depth", 2)):
+        n = 64
+
+        def one():
+            with torch.cuda.stream(st):
+                for k in range(n):
+                    o = (k % 16) * 4 * W * H
+                    dst_c[o:o + 4 * W * H].copy_(src[:4 * W * H], non_blocking=True)
+                    if planes == 2:
+                        dst_d[o:o + 4 * W * H].copy_(src[4 * W * H:], non_blocking=True)
+                st.synchronize()
+        fps, _ = e.timed(one, n)
+        res[name] = {"frames_per_s": fps, "gbs_aggregate": fps * planes * 4 * W * H / 1e9}
+    return res
+
+
+def parity_check(r, v, i, m, W, H, depth_test):
+    """One frame of the product path against the oracle (bit-exact colour and depth).  The oracle is the checker here."""
+    from oracle import oracle as O
+    c, d = r.render_views(np.asarray(m)[None], W, H)
+    rc, oc, od, _ = O.render(v, i, m, W, H, flags=O.DEPTH_LESS if depth_test else 0)
+    return bool(rc == 0 and np.array_equal(c[0], oc) and np.array_equal(d[0].view(np.uint32), od.view(np.uint32)))
+
+
+def workload_record(name, depth_test, local, dev, stream, flush, K=20, Wm=5):
+    """One entry of the `workloads` sub-record: device-resident frames/s, frame roofline, batch e2e and a parity bit."""
+    import torch
+    import software_renderer_b200 as srb
+    desc, W, H, v, i, xf = make_workload(name)
+    ntris, nverts = i.size // 3, int(v.shape[0])
+    with srb.CudaRenderer(local) as r:
+        r.depth_test = bool(depth_test)
+        r.set_mesh(v, i)
+        color = torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
+        depth = torch.empty((H, W), dtype=torch.float32, device=dev)
+        per_frame, launches, _ = device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, 0, dev)
+        acc = kernel_split(r, xf, W, H, color, depth, stream, flush, 0, dev, reps=3)
+        frame_ms = float(per_frame.mean())
+        CH = 8
+        bc = r.host_array((CH, H, W, 4), np.uint8)
+        bd = r.host_array((CH, H, W), np.float32)
+        mats = np.stack([xf(Wm + k) for k in range(CH)])
+        r.render_views(mats, W, H, color_out=bc, depth_out=bd)
+        t0 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t0 < 0.25:
+            r.render_views(mats, W, H, color_out=bc, depth_out=bd)
+            reps += 1
+        e2e = CH * reps / (time.perf_counter() - t0)
+        ok = parity_check(r, v, i, xf(3), W, H, depth_test)
+        stats = r.stats()
+    return {"config": workload_config(desc, W, H, ntris, nverts, depth_test), "value": 1000.0 / frame_ms, "unit": "frames/s",
+            "ms_per_step": frame_ms, "steps": K, "gtri_per_s": ntris / frame_ms / 1e6,
+            "frame_roofline": frame_roofline_of(frame_ms, ntris, nverts, W, H),
+            "roofline": roofline_of(acc, ntris, nverts, W, H, name + ("_depth" if depth_test else "")),
+            "kernel_ms": acc, "e2e": {"value": e2e, "unit": "frames/s", "api": "sr_render_batch, 8 frames per call, page-locked images"},
+            "parity_vs_oracle": ok, "gpu_launches_per_frame": launches // K,
+            "stats_last_frame": {k: (int(x) if k != "gpu_ms" else float(x)) for k, x in stats.items()}}
+
+
+def cfg5_leg(local, rank, world, dev, nviews=4096, per_rank_chunk=128):
+    """BASELINE.json configs[4]: 4096 camera views of the 1M-triangle cube-sphere at 512x512, sharded over the ranks (no
+    exchange while rendering), (i) left on the GPUs, (ii) gathered to rank 0 through sr_gather (NCCL send/recv on the
+    context's gather stream) with the gather of chunk k overlapping the rendering of chunk k+1.  Device time, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    import software_renderer_b200 as srb
+    from software_renderer_b200.multi_gpu import gather_views, init_comm, max_over_ranks, shard_range
+    desc, W, H, v, i, xf = make_workload("views512")
+    from software_renderer_b200 import scene as S
+    views = S.fibonacci_views(nviews)
+    ntris, nverts = i.size // 3, int(v.shape[0])
+    C = per_rank_chunk * world                           # views per chunk, all ranks together
+    nchunks = (nviews + C - 1) // C
+    stream = torch.cuda.Stream(device=dev)
+    with srb.CudaRenderer(local) as r:
+        r.set_mesh(v, i)
+        if world > 1:
+            init_comm(r)
+        color = [torch.empty((per_rank_chunk, H, W, 4), dtype=torch.uint8, device=dev) for _ in range(2)]
+        depth = [torch.empty((per_rank_chunk, H, W), dtype=torch.float32, device=dev) for _ in range(2)]
+        full_c = torch.empty((nviews, H, W, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
+        full_d = torch.empty((nviews, H, W), dtype=torch.float32, device=dev) if rank == 0 else None
+
+        def run(gather: bool):
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                dist.barrier()
+            with torch.cuda.stream(stream):
+                ev0.record(stream)
+                for k in range(nchunks):
+                    base, n_all = k * C, min(C, nviews - k * C)
+                    lo, hi = shard_range(n_all, rank, world)
+                    b = k & 1
+                    if gather:
+                        r.gather_fence(2 * b, stream.cuda_stream)        # the gathers that read this buffer pair two chunks ago
+                        r.gather_fence(2 * b + 1, stream.cuda_stream)
+                    if hi > lo:
+                        r.render_device(views[base + lo:base + hi], W, H, color[b].data_ptr(), depth[b].data_ptr(),
+                                        stream=stream.cuda_stream, sync=False)
+                    if gather and world > 1:
+                        gather_views(r, color[b][:hi - lo], n_all, full_c[base:base + n_all] if rank == 0 else None, slot=2 * b, stream=stream.cuda_stream)
+                        gather_views(r, depth[b][:hi - lo], n_all, full_d[base:base + n_all] if rank == 0 else None, slot=2 * b + 1, stream=stream.cuda_stream)
+                    elif gather:                                         # one GPU: the "composite" is a device copy
+                        full_c[base:base + n_all].copy_(color[b][:n_all], non_blocking=True)
+                        full_d[base:base + n_all].copy_(depth[b][:n_all], non_blocking=True)
+                if gather:
+                    for slot in range(4):
+                        r.gather_fence(slot, stream.cuda_stream)
+                ev1.record(stream)
+            r.sync()
+            if gather:
+                r.gather_sync()
+            torch.cuda.synchronize(dev)
+            return max_over_ranks(ev0.elapsed_time(ev1), device=dev)
+
+        run(False)                                       # warm-up (policies, buffers)
+        ms_render = min(run(False), run(False))
+        run(True)
+        ms_gather = min(run(True), run(True))
+        parity = None
+        if rank == 0:
+            # composite against the oracle on views spread over the whole list (each rank's shard is hit)
+            from oracle import oracle as O
+            picks = sorted(set(int(x) for x in np.linspace(0, nviews - 1, 32)))
+            parity = True
+            for k in picks:
+                rc, oc, od, _ = O.render(v, i, views[k], W, H)
+                parity &= bool(rc == 0 and np.array_equal(full_c[k].cpu().numpy(), oc) and
+                               np.array_equal(full_d[k].cpu().numpy().view(np.uint32), od.view(np.uint32)))
+        if world > 1:
+            r.comm_destroy()
+    per_view = 8 * W * H
+    remote = per_view * (nviews - (nviews + world - 1) // world) if world > 1 else 0       # bytes that cross NVLink into rank 0
+    return {"config": workload_config(desc, W, H, ntris, nverts, False), "views": nviews, "views_per_chunk_per_rank": per_rank_chunk,
+            "value": nviews / (ms_render / 1000.0), "unit": "views/s", "ms_total": ms_render,
+            "frame_roofline": frame_roofline_of(ms_render / nviews * world, ntris, nverts, W, H),
+            "gathered": {"value": nviews / (ms_gather / 1000.0), "unit": "views/s", "ms_total": ms_gather,
+                         "gather_overhead_ms": ms_gather - ms_render, "bytes_into_rank0": remote,
+                         "ingest_gbs_if_unhidden": (remote / 1e9) / max((ms_gather - ms_render) / 1000.0, 1e-9) if world > 1 and ms_gather > ms_render else None,
+                         "ingest_gbs_over_whole_run": (remote / 1e9) / (ms_gather / 1000.0),
+                         "api": "sr_gather (grouped ncclSend/ncclRecv on the context's gather stream), chunk k gathered while chunk k+1 renders",
+                         "composite_parity_vs_oracle_32_views": parity}}
+
+
 def run_cuda(args):
     import torch
     import torch.distributed as dist
     import software_renderer_b200 as srb
-    from software_renderer_b200 import scene as S
     from software_renderer_b200.multi_gpu import max_over_ranks
 
     rank = int(os.environ.get("RANK", "0"))
@@ -222,119 +561,23 @@ def run_cuda(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     # every rank renders its own frames: frame index = rank * (K + Wm) + step
     frame0 = rank * (K + Wm + 8)
-
-    def frame(k):
-        r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream, sync=False)
-
-    with torch.cuda.stream(stream):
-        frame(0)
-        r.sync()                                        # lets the adaptive batching policy settle
-        for k in range(1, Wm):
-            frame(k)
-        r.sync()
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        sampler = ClockSampler(local)
-        sampler.start()
-        t_wall0 = time.perf_counter()
-        launches = 0
-        for k in range(K):
-            if not os.environ.get("SR_BENCH_NOFLUSH"):
-                flush.fill_(k & 0xFF)                   # L2 flush between timed frames (not timed)
-            evs[k][0].record(stream)
-            frame(Wm + k)                               # asynchronous; calls accumulate, no host round trip
-            evs[k][1].record(stream)
-        r.sync()                                        # one status read-back for all K frames
-        launches = r.stats()["gpu_launches"]
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        t_wall = time.perf_counter() - t_wall0
-        clocks = sampler.stop()
-    per_frame = np.array([a.elapsed_time(b) for a, b in evs])         # this rank's frames, ms each
-    dev_ms = float(per_frame.sum())
-    dev_ms = max_over_ranks(dev_ms, device=dev)
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    per_frame, launches, t_wall = device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, frame0, dev)
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    dev_ms = max_over_ranks(float(per_frame.sum()), device=dev)
     value = world * K / (dev_ms / 1000.0)
 
-    # ---- e2e: host-pointer C-ABI calls, pinned host images; H2D of the transform and D2H of both images are inside
-    # the timed region.  (a) sr_render: one synchronous call per frame, the strict drop-in for render(renderPass:);
-    # (b) sr_render_batch: the same frames handed over 16 at a time, D2H of frame i overlapped with frame i+1.
-    hc = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
-    hd = torch.empty((H, W), dtype=torch.float32).pin_memory()
-    rp = srb.RenderPass(srb.Image(hc.numpy(), W, H), srb.Image(hd.numpy(), W, H), v, i, srb.PrimitiveType.triangle, None)
-    r._mesh_key = (v, i)                                # mesh already uploaded (static across frames)
-    for k in range(max(3, Wm)):
-        rp.transform = xf(frame0 + k)
-        r.render(rp)
-
-    def timed_passes(one_pass):
-        """The K e2e frames are repeated until the wall-clock region is ~0.3 s (a 1080p frame takes 0.3 ms, a 512x512
-        view 0.05 ms: K = 100 frames alone would be a region of a few ms, at the mercy of one scheduler hiccup on
-        one of N ranks).  Returns whole-job frames/s (max over ranks of the wall time) and the pass count."""
-        t0 = time.perf_counter()
-        one_pass()
-        passes = int(min(200, max(1, np.ceil(0.3 / max(time.perf_counter() - t0, 1e-4)))))
-        passes = int(max_over_ranks(float(passes), device=dev))          # the same count on every rank
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
-        for _ in range(passes):
-            one_pass()
-        t = max_over_ranks(time.perf_counter() - t0, device=dev)
-        return world * K * passes / t, passes
-
-    def sync_pass():
-        for k in range(K):
-            rp.transform = xf(frame0 + Wm + k)
-            r.render(rp)
-
-    e2e_sync, sync_passes = timed_passes(sync_pass)
-    CH = 16
-    bc = torch.empty((CH, H, W, 4), dtype=torch.uint8).pin_memory()
-    bd = torch.empty((CH, H, W), dtype=torch.float32).pin_memory()
-    mats = np.stack([xf(frame0 + Wm + k) for k in range(K)])
-    r.render_views(mats[:min(K, CH)], W, H, color_out=bc.numpy(), depth_out=bd.numpy())      # warm-up
-
-    def batch_pass():
-        for s0 in range(0, K, CH):
-            n = min(CH, K - s0)
-            r.render_views(mats[s0:s0 + n], W, H, color_out=bc.numpy()[:n], depth_out=bd.numpy()[:n])
-
-    e2e_value, batch_passes = timed_passes(batch_pass)
+    e2e = e2e_suite(r, local, world, dev, v, i, xf, W, H, K, Wm, frame0, full=(world == 1 and not args.quick))
 
     line = None
     if rank == 0:
-        # per-kernel split of one frame (extra events between kernels; separate from the timed loop)
-        r.set_profiling(True)
-        acc = {}
-        reps = 5
-        for k in range(reps):
-            flush.fill_(1)
-            torch.cuda.synchronize(dev)
-            r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream)
-            for nm, ms in r.kernel_times().items():
-                acc[nm] = acc.get(nm, 0.0) + ms / reps
-        r.set_profiling(False)
+        acc = kernel_split(r, xf, W, H, color, depth, stream, flush, frame0, dev)
         stats = r.stats()
-        hbm, peak_kind = peaks()
-        # algorithmic bytes (SURVEY.md §8(d)): indices 12 B/tri, vertex xyz+rgb 24 B, colour+depth 8 B/pixel, split over
-        # the kernels that touch them (DESIGN.md §5)
-        alg = {"k_transform": 12 * nverts, "k_setup": 12 * ntris, "k_tile": 12 * nverts + 8 * W * H,
-               "k_resolve": 12 * nverts + 8 * W * H}
-        top = max(acc, key=acc.get) if acc else "k_tile"
-        top_ms = acc.get(top, float("nan"))
-        top_bytes = alg.get(top, 0)
-        achieved = top_bytes / (top_ms * 1e-3) / 1e9 if top_ms and top_ms == top_ms else float("nan")
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            try:
-                traffic = json.load(open(tp)).get(args.workload + ("_depth" if args.depth_test else ""), {}).get(top)
-            except Exception:
-                traffic = None
-        frame_bytes = S.algorithmic_bytes(ntris, nverts, W, H)
         frame_ms = dev_ms / K
         # CPU baseline: the oracle on one host core (the reference loop is sequential, Renderer.swift:222), about 10 s
         # of CPU work: calibrate on a 1/8 sample, then whole frames (or the largest 1/stride sample that fits)
@@ -344,41 +587,45 @@ def run_cuda(args):
         stride = 1
         while full_s / stride > 15.0:
             stride *= 2
-        nframes = int(max(1, min(2000, 10.0 / max(full_s / stride, 1e-4))))
+        nframes = int(max(1, min(2000, (3.0 if args.quick else 10.0) / max(full_s / stride, 1e-4))))
         t_cpu = time_oracle(v, i, xf, W, H, 1, nframes, stride, bool(args.depth_test))
         cpu_value = (nframes / stride) / t_cpu
         line = {
             "metric": "frames_per_second", "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32+i64", "data": "synthetic",
-            "config": {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": nverts,
-                       "depth_test": bool(args.depth_test), "l2": "flushed between timed frames (256 MiB fill)",
-                       "parallelism": f"{world} independent view streams, one per GPU"},
+            "config": workload_config(desc, W, H, ntris, nverts, args.depth_test),
+            "run": {"l2": "flushed between timed frames (256 MiB fill)", "parallelism": f"{world} independent view streams, one per GPU, no data-path collective"},
             "gtri_per_s": value * ntris / 1e9,
             "frame_ms_rank0": {"median": float(np.median(per_frame)), "p10": float(np.percentile(per_frame, 10)),
                                "p90": float(np.percentile(per_frame, 90))},
-            "frame_roofline": {"bound": "hbm", "achieved": frame_bytes / (frame_ms * 1e-3) / 1e9, "peak": hbm,
-                               "unit": "GB/s", "frac": frame_bytes / (frame_ms * 1e-3) / 1e9 / hbm,
-                               "bytes_per_frame": frame_bytes, "peak_kind": peak_kind},
-            "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                         "frac": achieved / hbm, "traffic": traffic, "algorithmic_bytes": top_bytes,
-                         "kernel_ms": top_ms, "peak_kind": peak_kind},
+            "frame_roofline": frame_roofline_of(frame_ms, ntris, nverts, W, H),
+            "roofline": roofline_of(acc, ntris, nverts, W, H, args.workload + ("_depth" if args.depth_test else "")),
             "kernel_ms": acc,
             "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": 1, "kind": "port",
                              "sample": f"{nframes} render pass(es) of every {stride}-th triangle ({ntris // stride} of {ntris} "
                                        f"tris, full clear) on 1 core, {t_cpu:.2f} s in total, each pass counted as 1/{stride} "
                                        f"frame; host has {cpu_count()} cores"},
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": 8 * W * H,
-                    "api": "sr_render_batch, 16 frames per call, pinned host images, mesh uploaded once by sr_set_mesh",
-                    "frames_timed_per_rank": K * batch_passes,
-                    "sync_per_frame": {"value": e2e_sync, "unit": "frames/s", "api": "sr_render, one synchronous call per frame",
-                                       "frames_timed_per_rank": K * sync_passes}},
+            "e2e": e2e,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "wall_s_timed_region": t_wall,
             "stats_last_frame": {k: (int(x) if k != "gpu_ms" else float(x)) for k, x in stats.items()},
         }
     r.close()
+    del color, depth
+    # the other BASELINE configs and the depth-tested mode, 20 timed frames each (rank 0 of the one-GPU run)
+    if world == 1 and not args.quick and args.workload == "soup1m" and not args.depth_test:
+        wl = {}
+        for key, (name, dt) in {"soup1m_depth": ("soup1m", True), "ico80k": ("ico80k", False), "cs10m4k": ("cs10m4k", False),
+                                "views512": ("views512", False)}.items():
+            wl[key] = workload_record(name, dt, local, dev, stream, flush)
+        line["workloads"] = wl
+    # configs[4], the multi-GPU configuration: sharded views, with and without the composite gather
+    if not args.quick and args.workload == "soup1m" and not args.depth_test:
+        c5 = cfg5_leg(local, rank, world, dev)
+        if line is not None:
+            line["cfg5_views512"] = c5
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -493,6 +740,7 @@ def main():
     ap.add_argument("--workload", default="soup1m", choices=sorted(WORKLOADS))
     ap.add_argument("--depth-test", type=int, default=0)
     ap.add_argument("--split-frame", type=int, default=0, help="1: every step is ONE frame split by rows over the ranks")
+    ap.add_argument("--quick", type=int, default=0, help="1: main line only (no e2e variants, no other workloads, no cfg5 leg): for kernel A/B runs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":

@@ -76,7 +76,7 @@ struct ViewStatus {
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define TL_BEGIN(st, slot) do { if (threadIdx.x == 0) atomicMax(&(st)->tl_launch_inv[slot], ~gtime()); } while (0)
 #define TL_GO(st, slot)    do { if (threadIdx.x == 0) atomicMax(&(st)->tl_go_inv[slot], ~gtime()); } while (0)
-#define TL_END(st, slot)   do { if (threadIdx.x == 0) atomicMax(&(st)->tl_end[slot], gtime()); } while (0)
+#define TL_END(st, slot)   do { if ((threadIdx.x & 31) == 0) atomicMax(&(st)->tl_end[slot], gtime()); } while (0)   /* every warp: thread 0 may finish long before its CTA */
 #else
 #define TL_BEGIN(st, slot) do {} while (0)
 #define TL_GO(st, slot)    do {} while (0)

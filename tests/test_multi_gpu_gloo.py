@@ -118,3 +118,60 @@ def test_banded_frame_gather_equals_whole_frame(tmp_path, world):
     got = np.load(path)
     want = _render_views(S.fibonacci_views(2))
     assert np.array_equal(got[:2], want) and np.array_equal(got[2], want[0])
+
+
+# ---- round 2: the host plumbing of sr_gather (the NCCL calls themselves need GPUs: tests/test_gather_gpu.py) ----------
+from software_renderer_b200.multi_gpu import init_comm, view_block_bytes  # noqa: E402
+
+
+def test_view_block_bytes_and_chunked_layout_is_view_order():
+    """bench.py / nccl_composite_check.py gather chunk by chunk: chunk k = views [kC, (k+1)C), split over the ranks by
+    shard_range; sr_gather lays rank r's block at the sum of the blocks before it, which must be view order."""
+    for nviews, world, per in ((4096, 8, 128), (37, 2, 5), (10, 4, 3), (5, 8, 1)):
+        C = per * world
+        order = []
+        for k in range((nviews + C - 1) // C):
+            base, n_all = k * C, min(C, nviews - k * C)
+            sizes = view_block_bytes(n_all, world, 7)
+            assert sum(sizes) == 7 * n_all and len(sizes) == world
+            for r in range(world):
+                lo, hi = shard_range(n_all, r, world)
+                assert sizes[r] == 7 * (hi - lo) and hi - lo <= per
+                order += list(range(base + lo, base + hi))
+        assert order == list(range(nviews))
+
+
+class _FakeRenderer:
+    """Stands in for CudaRenderer in init_comm: the id comes from 'rank 0's library', every rank must receive it."""
+    made = 0
+
+    @staticmethod
+    def comm_unique_id():
+        _FakeRenderer.made += 1
+        return bytes(range(128))
+
+    def comm_init(self, uid, rank, world):
+        self.args = (uid, rank, world)
+
+
+def _comm_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        r = _FakeRenderer()
+        init_comm(r)
+        assert r.args == (bytes(range(128)), rank, world)
+        assert _FakeRenderer.made == (1 if rank == 0 else 0)       # only the root asks the library for an id
+        open(os.path.join(out_dir, f"ok{rank}"), "w").close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_init_comm_hands_rank0s_id_to_every_rank(tmp_path):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_comm_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")

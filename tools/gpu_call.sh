@@ -1,10 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-export SR_COMPACT=0 SR_LIB=scratch/libsr_cuda_tl.so
-echo "pdl on, flush";   python bench.py --steps 4 --warmup 3 2>&1 >/dev/null | grep "^view" | tail -2
-echo "pdl off, flush";  SR_PDL=0 python bench.py --steps 4 --warmup 3 2>&1 >/dev/null | grep "^view" | tail -2
-echo "pdl on, noflush"; SR_BENCH_NOFLUSH=1 python bench.py --steps 4 --warmup 3 2>&1 >/dev/null | grep "^view" | tail -2
-echo "pdl off, noflush"; SR_PDL=0 SR_BENCH_NOFLUSH=1 python bench.py --steps 4 --warmup 3 2>&1 >/dev/null | grep "^view" | tail -2
-unset SR_LIB
-SR_BENCH_NOFLUSH=1 python bench.py --steps 100 --warmup 20 > gpurun_out/c5_bench_noflush.json 2>/dev/null
-python profiles/show.py gpurun_out/c5_bench_*.json | grep -v stats
+python tools/dump_mesh.py soup1m /tmp/soup.bin 64
+export SR_COMPACT=0
+echo "== native loop, default lib"; scratch/native_loop software_renderer_b200/libsr_cuda.so /tmp/soup.bin 1920 1080 100
+echo "== native loop, PDL off"; SR_PDL=0 scratch/native_loop software_renderer_b200/libsr_cuda.so /tmp/soup.bin 1920 1080 100
+echo "== native loop, TL lib"; scratch/native_loop scratch/libsr_cuda_tl.so /tmp/soup.bin 1920 1080 4 2>&1 | grep -E "^view|native" | tail -3
+echo "== native loop, TL lib, PDL off"; SR_PDL=0 scratch/native_loop scratch/libsr_cuda_tl.so /tmp/soup.bin 1920 1080 4 2>&1 | grep -E "^view|native" | tail -3
+echo "== python, TL lib"; SR_LIB=scratch/libsr_cuda_tl.so python bench.py --steps 4 --warmup 3 2>&1 >/dev/null | grep "^view" | tail -2

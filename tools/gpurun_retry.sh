@@ -1,0 +1,9 @@
+#!/bin/bash
+# usage: tools/gpurun_retry.sh <log> <gpurun args...>   retries while the pod answers "transient" (nothing charged)
+log=$1; shift
+for try in $(seq 1 40); do
+  /usr/local/graft/bin/gpurun "$@" > "$log" 2>&1
+  if ! grep -q "status=transient" "$log"; then break; fi
+  sleep 45
+done
+echo "[retry] finished after $try attempt(s)" >> "$log"
