@@ -202,8 +202,14 @@ def device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, frame0, dev):
     """K timed frames, device resident, L2 flushed between frames; returns (per-frame ms array, launches, wall s)."""
     import torch
 
+    # matrices converted up front: the enqueue loop must stay ahead of a 0.06 - 0.2 ms frame (with numpy building a
+    # matrix per iteration it did not: 0.43 ms of host time per frame, the kernels of a frame were submitted just in time
+    # and programmatic dependent launch had nothing to overlap)
+    mats = [r.colmajor(xf(frame0 + k)) for k in range(Wm + K)]
+    cptr, dptr, sptr = color.data_ptr(), depth.data_ptr(), stream.cuda_stream
+
     def frame(k):
-        r.render_device(xf(frame0 + k), W, H, color.data_ptr(), depth.data_ptr(), stream=stream.cuda_stream, sync=False)
+        r.render_device(mats[k], W, H, cptr, dptr, stream=sptr, sync=False, colmajor=True)
 
     with torch.cuda.stream(stream):
         frame(0)

@@ -362,16 +362,24 @@ class CudaRenderer:
         return color, depth
 
     def render_device(self, transforms, width: int, height: int, color_ptr: int, depth_ptr: int | None,
-                      primitive_type=PrimitiveType.triangle, stream: int | None = None, sync: bool = True):
+                      primitive_type=PrimitiveType.triangle, stream: int | None = None, sync: bool = True,
+                      colmajor: bool = False):
         """Device-resident variant: `color_ptr` / `depth_ptr` are CUDA device addresses (e.g. torch tensors'
-        data_ptr()) for n consecutive images; `stream` is a cudaStream_t handle or None."""
-        m = _colmajor(np.asarray(transforms, dtype=np.float32).reshape(-1, 4, 4))
+        data_ptr()) for n consecutive images; `stream` is a cudaStream_t handle or None.  colmajor=True: `transforms`
+        already is the (n, 16) float32 array CudaRenderer.colmajor() returns."""
+        m = transforms if colmajor else _colmajor(np.asarray(transforms, dtype=np.float32).reshape(-1, 4, 4))
         rc = self._lib.sr_render_device(self._ctx, m.ctypes.data, m.shape[0], int(primitive_type), width, height,
                                         ctypes.c_void_p(color_ptr), ctypes.c_void_p(depth_ptr) if depth_ptr else None,
                                         self._flags(depth_ptr is not None), ctypes.c_void_p(stream) if stream else None)
         self._check(rc)
         if sync:
             self.sync()
+
+    @staticmethod
+    def colmajor(transforms) -> np.ndarray:
+        """(n, 16) float32 column-major copies of (n, 4, 4) / (4, 4) matrices, the layout the C ABI takes: convert once,
+        then enqueue with render_device(..., colmajor=True) from a loop that must stay ahead of the GPU."""
+        return _colmajor(np.asarray(transforms, dtype=np.float32).reshape(-1, 4, 4))
 
     def sync(self):
         self._check(self._lib.sr_sync(self._ctx))

@@ -1,11 +1,12 @@
 // native_loop.cu — the timed loop of bench.py without Python or torch in the process: sr_render_device in a loop on
 // this program's own stream, L2 flushed between frames, CUDA events per frame.  Used to tell what the host process
 // contributes to the holes between a frame's kernels.
-//   native_loop <lib.so> <mesh.bin> W H frames     mesh.bin: u64 nverts, u64 nidx, float32[nverts*8], int64[nidx], u64 nmats, float32[nmats*16] (column-major)
+//   native_loop <lib.so> <mesh.bin> W H frames [host lag us]     mesh.bin: u64 nverts, u64 nidx, float32[nverts*8], int64[nidx], u64 nmats, float32[nmats*16] (column-major)
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
 #include <dlfcn.h>
+#include <unistd.h>
 #include <cuda_runtime.h>
 #include "../../include/sr_cuda.h"
 int main(int argc, char** argv) {
@@ -31,7 +32,9 @@ int main(int argc, char** argv) {
     for (int k = 0; k < 6; ++k) { p_sr_render_device(c, &mats[16 * (k % nm)], 1, SR_TRIANGLE, W, H, color, depth, 0, st); p_sr_sync(c); }
     std::vector<cudaEvent_t> e0(frames), e1(frames);
     for (int k = 0; k < frames; ++k) { cudaEventCreate(&e0[k]); cudaEventCreate(&e1[k]); }
+    const int lag_us = argc > 6 ? atoi(argv[6]) : 0;   // host-bound emulation: sleep before every frame's submission
     for (int k = 0; k < frames; ++k) {
+        if (lag_us) { cudaStreamSynchronize(st); usleep(lag_us); }
         cudaMemsetAsync(flush, k & 0xff, 256u << 20, st);
         cudaEventRecord(e0[k], st);
         p_sr_render_device(c, &mats[16 * ((6 + k) % nm)], 1, SR_TRIANGLE, W, H, color, depth, 0, st);
