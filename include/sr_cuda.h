@@ -81,6 +81,8 @@ typedef struct sr_stats {
     uint64_t batches_run;     /* index-descending batches that still had open tiles (0 = single-batch frame) */
     uint64_t depth_culled;    /* depth mode: tile-list records rejected by their depth bound or never read */
     uint64_t nobin_reruns;    /* frames launched without the binning kernels that met a large triangle and were re-run */
+    uint64_t depth_two_pass_frames; /* depth mode: views rendered as a front pass + a culled back pass */
+    uint64_t back_survivors;  /* depth mode, two-pass views: triangles of the back pass that were not culled */
     uint64_t gpu_launches;    /* kernels launched by the call */
     float    gpu_ms;          /* device time of the call's kernels, CUDA events on the context's stream */
 } sr_stats;

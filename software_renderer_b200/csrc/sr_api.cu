@@ -205,7 +205,7 @@ struct sr_ctx {
     double first_frac = 0.125;           // batched frames: share of the primitives (from the top) in the first batch
     int force_batches = -1;              // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     bool use_pdl = true;
-    bool use_compact = true;             // SR_COMPACT=0: late batches run the one-triangle-per-thread k_setup
+    bool use_compact = false;            // SR_COMPACT=1: late batches of depth-off frames run the compacting k_setup (measured: slower)
     // speculative frames without the binning kernels: enabled after a frame in which no triangle was large; a frame
     // that does meet a large triangle only counts it and is re-run with the full pipeline (results identical)
     bool nobin_mode = false, call_nobin = false, allow_nobin = true;   // SR_NOBIN=0 disables
@@ -213,6 +213,17 @@ struct sr_ctx {
     // overflows makes the host double the capacity and re-run the frame; past kSlabLimit bytes the context falls
     // back to compact lists (scan + fill) for good.  SR_SLAB=0 forces compact lists.
     float z_lo = 0.0f, z_hi = 1.0f;      // depth mode: range of the triangles' depth bounds seen last frame (chunk thresholds)
+    // two-pass depth frames (front pass, then the back pass culled against the front pass's per-tile farthest depth): a
+    // launch policy like the others - chosen from the previous frame's counters, never changes the image
+    bool depth_two_pass = false;
+    int force_zpass = 0;                 // SR_ZPASS env: 0 = never (default), 1 = always, -1 = adaptive.  Default off: measured on the
+                                         //   1M soup the two passes are bit-exact but SLOWER (1,914 vs 2,128 frames/s): k_setup 286 -> 202 us,
+                                         //   k_tile 203 -> 303 us (the second tile pass costs more than the binning it saves)
+    double zfrac = 0.125;                // SR_ZFRAC: share of the triangles (nearest corner first) the front pass takes
+    float zsplit = 0.25f, zh_lo = 0.0f, zh_hi = 1.0f;   // split depth; range of the min-corner-depth histogram
+    bool zsplit_valid = false;
+    unsigned long long single_pass_pairs = 0;
+    DevBuf<unsigned> tile_zmax;
     bool slab_mode = true;
     unsigned slab_cap = 32, call_slab_cap = 0;
     size_t last_ntiles = 0;
@@ -339,6 +350,7 @@ void set_frame_carveouts(int pct) {
     set_carveout(k_setup<true, false, false>, pct);  set_carveout(k_setup<true, true, false>, pct);
     set_carveout(k_setup<false, false, false>, pct); set_carveout(k_setup<false, true, false>, pct);
     set_carveout(k_setup<false, true, true>, pct);   set_carveout(k_setup<false, true, true, true>, pct);
+    set_carveout(k_setup<true, true, false, true>, pct); set_carveout(k_tile<true, true>, pct);
     set_carveout(k_scan, pct); set_carveout(k_bin_fill, pct);
     set_carveout(k_tile<true, false>, pct); set_carveout(k_tile<false, false>, pct); set_carveout(k_tile<false, true>, pct);
     set_carveout(k_resolve<true, 1>, pct); set_carveout(k_resolve<true, 4>, pct);
@@ -394,6 +406,7 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
     }
     if (!c->slab_mode) { int rc = ensure_compact(c); if (rc) return rc; }
     if (depth_mode) {
+        SR_CUDA(c, c->tile_zmax.reserve(tiles));
         SR_CUDA(c, c->ztri.reserve(std::max<size_t>(c->nidx / 3, 1)));
         if (npx > c->vis64.cap) {
             SR_CUDA(c, c->vis64.reserve(npx));
@@ -461,6 +474,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
         for (int q = 1; q < NCHUNK - 1; ++q) fp.zthr[q] = std::max(fp.zthr[q], fp.zthr[q - 1]);      // ascending, whatever the rounding
         fp.nobin = (c->nobin_mode && c->allow_nobin && !fp.batched) ? 1 : 0;
         if (fp.nobin) c->call_nobin = true;
+        fp.tile_zmax = c->tile_zmax.p;
+        const bool two_pass = depth_mode && c->depth_two_pass && fp.slab_cap > 0 && !fp.nobin && ntris >= (1 << 16);
         const int ncnt = fp.ntiles * NCHUNK;
         BatchParams batches[MAX_BATCHES];
         int nb = 0;
@@ -470,6 +485,11 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
             const int first = std::min(ntris - 1, std::max(1, (int)((double)ntris * c->first_frac)));
             batches[nb++] = BatchParams{ntris - first, ntris, 0, 0, 0};
             batches[nb++] = BatchParams{0, ntris - first, 0, 1, 1};
+        } else if (two_pass) {
+            if (!c->zsplit_valid) { c->zsplit = c->zh_lo + 0.25f * (c->zh_hi - c->zh_lo); c->zsplit_valid = true; }
+            const float scale = c->zh_hi > c->zh_lo ? (float)ZHIST_BINS / (c->zh_hi - c->zh_lo) : 0.0f;
+            batches[nb++] = BatchParams{0, ntris, 0, 0, 0, 1, c->zsplit, c->zh_lo, scale};
+            batches[nb++] = BatchParams{0, ntris, 0, 1, 1, 2, c->zsplit, c->zh_lo, scale};
         } else {
             batches[nb++] = BatchParams{0, ntris, 0, 0, 1};
         }
@@ -482,8 +502,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
                 prof_mark(c, st, "k_setup");
                 // later batches of a batched frame mostly meet retired tiles: the compacting variant (cheap test first,
                 // full setup on the survivors with dense warps)
-                const bool compact = fp.batched && b > 0 && c->use_compact;
-                auto ks = depth_mode ? (fp.nobin ? k_setup<true, false, false> : k_setup<true, true, false>)
+                const bool compact = (fp.batched && b > 0 && c->use_compact) || two_pass;
+                auto ks = depth_mode ? (fp.nobin ? k_setup<true, false, false> : (two_pass ? k_setup<true, true, false, true> : k_setup<true, true, false>))
                                      : (fp.nobin ? k_setup<false, false, false>
                                                  : (fp.batched ? (compact ? k_setup<false, true, true, true> : k_setup<false, true, true>)
                                                                : k_setup<false, true, false>));
@@ -520,9 +540,11 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
             }
             prof_mark(c, st, "k_tile");
             // late batches mostly find retired tiles: a persistent grid avoids thousands of empty CTA launches
-            const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u) : (unsigned)fp.ntiles;
+            const unsigned tgrid = (fp.batched && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 6u)
+                                 : ((two_pass && b > 0) ? std::min<unsigned>(fp.ntiles, 148u * 4u) : (unsigned)fp.ntiles);
             const TriRec* tile_recs = fp.slab_cap ? c->slab.p : c->recs.p;
-            auto kt = depth_mode ? k_tile<true, false> : ((fp.batched && b > 0) ? k_tile<false, true> : k_tile<false, false>);   // batches: depth off only
+            auto kt = depth_mode ? ((two_pass && b > 0) ? k_tile<true, true> : k_tile<true, false>)
+                                 : ((fp.batched && b > 0) ? k_tile<false, true> : k_tile<false, false>);
             launch_pdl(c, kt, tgrid, 256, st, fp, bp, in, tile_recs, c->cursor.p, c->counts.p, c->pairs.p, c->vis32.p, c->vis64.p, c->tile_done.p, d_status, color32, depth_dev);
             c->launches++;
         }
@@ -623,6 +645,10 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
         c->stats.pairs_consumed += s.pairs_consumed;
         c->stats.depth_culled += s.pairs_culled;
         c->stats.batches_run += s.batches_run;
+        c->stats.back_survivors += s.back_survivors;
+        unsigned hist_total = 0;
+        for (int q = 0; q < ZHIST_BINS; ++q) hist_total += s.zhist[q];
+        if (hist_total) c->stats.depth_two_pass_frames++;
     }
     // adaptive policy for the next call (results are identical either way): batch when most list entries of a
     // single-batch frame were never read; go back when batching did not retire the frame early
@@ -639,6 +665,32 @@ void accumulate_stats(sr_ctx* c, size_t nviews, int prim) {
             }
         }
         const ViewStatus& s = c->h_status[nviews - 1];
+        {   // two-pass depth frames: on when most list entries of a single-pass frame were never used; the split depth is
+            // the zfrac quantile of the nearest-corner depths, from the front pass's histogram
+            unsigned long long hist_total = 0, pairs = 0;
+            for (int q = 0; q < ZHIST_BINS; ++q) hist_total += s.zhist[q];
+            for (int b = 0; b < MAX_BATCHES; ++b) pairs += s.total_pairs[b];
+            const bool was_two_pass = hist_total != 0;
+            if (was_two_pass) {
+                unsigned long long cum = 0;
+                const double target = c->zfrac * (double)hist_total;
+                int bin = 0;
+                while (bin < ZHIST_BINS - 1 && (double)(cum + s.zhist[bin]) < target) cum += s.zhist[bin++];
+                // inside the bin: linear
+                const double inbin = s.zhist[bin] ? std::min(1.0, std::max(0.0, (target - (double)cum) / (double)s.zhist[bin])) : 1.0;
+                c->zsplit = c->zh_lo + (c->zh_hi - c->zh_lo) * (float)(((double)bin + inbin) / ZHIST_BINS);
+                c->zsplit_valid = true;
+                if (c->force_zpass < 0 && c->single_pass_pairs && pairs * 2 > c->single_pass_pairs) c->depth_two_pass = false;   // not saving list entries
+            } else if (s.total_pairs[0] && (s.pairs_culled || s.pairs_consumed)) {          // a single-pass depth frame
+                c->single_pass_pairs = s.total_pairs[0];
+                if (c->force_zpass < 0) c->depth_two_pass = s.total_pairs[0] >= (1u << 18) && s.pairs_culled * 2 > s.total_pairs[0];
+                if (!c->zsplit_valid) { c->zh_lo = c->z_lo; c->zh_hi = c->z_hi; }
+            }
+            if (c->force_zpass >= 0) c->depth_two_pass = c->force_zpass != 0;
+            // the histogram range only ever grows (a wider range costs resolution, not correctness)
+            if (c->z_lo < c->zh_lo) c->zh_lo = c->z_lo;
+            if (c->z_hi > c->zh_hi) c->zh_hi = c->z_hi;
+        }
         if (c->force_batches >= 0) c->batched_mode = c->force_batches != 0;
         else if (!c->batched_mode) {
             c->single_batch_pairs = s.total_pairs[0];
@@ -759,6 +811,8 @@ int sr_create(sr_ctx** out, int device) {
         set_frame_carveouts(pct);
         cudaGetLastError();
     }
+    if (const char* e = getenv("SR_ZPASS")) { c->force_zpass = atoi(e); c->depth_two_pass = c->force_zpass > 0; }
+    if (const char* e = getenv("SR_ZFRAC")) c->zfrac = std::min(0.9, std::max(0.005, atof(e)));
     if (const char* e = getenv("SR_COMPACT")) c->use_compact = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB")) c->slab_mode = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB_CAP")) c->slab_cap = std::max(1, atoi(e));
@@ -795,6 +849,7 @@ void sr_destroy(sr_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release(); c->slab.release(); c->ztri.release();
+    c->tile_zmax.release();
     c->counts.release(); c->cursor.release(); c->pairs.release(); c->vis32.release(); c->vis64.release();
     c->look.release(); c->ticket.release(); c->status.release(); c->tile_done.release(); c->done_bits.release();
     for (int i = 0; i < 2; ++i) {
@@ -870,6 +925,10 @@ int sr_set_mesh(sr_ctx* c, const sr_vertex* vertices, size_t nverts, const int64
         c->single_batch_pairs = 0;
         c->nobin_mode = false;
         c->z_lo = 0.0f; c->z_hi = 1.0f;
+        c->depth_two_pass = c->force_zpass > 0;
+        c->zsplit_valid = false;
+        c->zh_lo = 0.0f; c->zh_hi = 1.0f;
+        c->single_pass_pairs = 0;
     }
     return SR_OK;
 }

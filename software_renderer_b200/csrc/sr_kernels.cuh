@@ -31,6 +31,7 @@ constexpr int SMALL_MAX = 8;         // direct path: clipped bbox at most SMALL_
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;        // per thread -> 2048 counters per CTA
 constexpr int TILE_BATCH = 16;
+constexpr int ZHIST_BINS = 64;
 #ifndef SR_SETUP_THREADS
 #define SR_SETUP_THREADS 256
 #endif       // k_setup CTA size.  Its warps are independent (all staging is per warp; no block barrier after the first
@@ -42,7 +43,7 @@ constexpr int TILE_BATCH = 16;
 #endif       // resident CTAs per SM asked of the binning k_setup variants (1280 threads: 47-48 registers)
 constexpr int SETUP_THREADS = SR_SETUP_THREADS;
 #ifndef SR_LATE_PT
-#define SR_LATE_PT 4
+#define SR_LATE_PT 2
 #endif       // triangles per thread in phase 1 of the compacting (late-batch) k_setup
 constexpr int LATE_PT = SR_LATE_PT;
 #ifndef SR_LATE_MINB
@@ -66,6 +67,8 @@ struct ViewStatus {
     unsigned open_after_first;          // batched mode: tiles still open after the first batch
     unsigned zlo_inv, zhi;              // depth mode: ~min / max of depth_ord(lower bound) over binned triangles
     unsigned long long pairs_culled;    // depth mode: records rejected by their depth bound or never read
+    unsigned zhist[ZHIST_BINS];         // two-pass depth frames: histogram of min corner depth over the on-screen triangles
+    unsigned back_survivors;            // two-pass depth frames: triangles of the back pass that were not culled
 #ifdef SR_TIMELINE
     // debug build: %globaltimer stamps per launch slot (2 * batch + {0 k_setup, 1 k_tile}): first CTA started,
     // first CTA past the grid dependency, last CTA finished.  Gives the overlapped timeline of a frame.
@@ -174,6 +177,8 @@ struct FrameParams {
                               //    triangle); a large triangle is only counted and the host re-runs the frame
     unsigned* done_bits;      // batched frames: one bit per retired tile, `wpr` words per tile row; all zero between
     int wpr;                  //   frames (set by k_tile when it retires a tile, cleared by the final batch's k_tile)
+    unsigned* tile_zmax;      // two-pass depth frames: per tile, depth_ord of the farthest pixel after the front pass
+                              //   (0xffffffff while a pixel of the tile is still empty)
 };
 
 // Retired-tile bitmap (batched frames).  It is constant while k_setup runs, so the loads may take the read-only path.
@@ -195,6 +200,15 @@ struct BatchParams {
     int chunk_shift;          // chunk = (prim - lo) >> chunk_shift  (< NCHUNK)
     int index;                // batch ordinal
     int final_batch;          // 1: every tile still open is shaded at the end of this batch
+    // Two-pass depth frames (SR_FLAG_DEPTH_LESS, heavy overdraw).  zpass 1 = front pass: only triangles whose nearest
+    // corner is in front of `zsplit` are set up, binned and rasterized; every tile is shaded, its final keys stay parked
+    // in vis64 and its farthest depth goes to tile_zmax.  zpass 2 = back pass: the other triangles, minus every one
+    // whose rigorous depth lower bound is behind all the tiles of its bounding box (it cannot pass the strict < of
+    // R:258 anywhere); tiles that receive anything are stamped in tile_done and redone by a persistent k_tile from the
+    // parked keys.  zpass 0 = the single pass.  The image is the same in all three.
+    int zpass;
+    float zsplit;
+    float zh_lo, zh_scale;    // histogram bin of a depth z: (z - zh_lo) * zh_scale, clamped to [0, ZHIST_BINS)
 };
 
 // Spreads `n` items per lane evenly over the warp: calls f(src_lane, item) once per item.  Source-lane data must
@@ -254,7 +268,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
-                                               float4* __restrict__ ztri, const unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
+                                               float4* __restrict__ ztri, unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status) {
     TL_BEGIN(status, 2 * bp.index);
     pdl_wait();
     TL_GO(status, 2 * bp.index);
@@ -276,36 +290,84 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
     const int wbase = threadIdx.x & ~31;
     int nsurv = 1;                                           // !COMPACT: the loop below runs once, one triangle per thread
     if (COMPACT) {
+        // Phase 1.  The loads of the thread's LATE_PT triangles are issued together (indices, then corners): the phase is
+        // two dependent memory round trips, so its throughput is the number of loads in flight.
+        __shared__ unsigned s_hist[DEPTH ? ZHIST_BINS : 1];
+        if (DEPTH && bp.zpass == 1) {
+            if (threadIdx.x < ZHIST_BINS) s_hist[threadIdx.x] = 0u;
+            __syncthreads();
+        }
         unsigned nskip = 0;
+        int pid[LATE_PT], ii[LATE_PT][3];
 #pragma unroll
         for (int k = 0; k < LATE_PT; ++k) {
-            const int p = bp.lo + (blockIdx.x * LATE_PT + k) * SETUP_THREADS + (int)threadIdx.x;
+            pid[k] = bp.lo + (blockIdx.x * LATE_PT + k) * SETUP_THREADS + (int)threadIdx.x;
+            const bool in = pid[k] < bp.hi;
+#pragma unroll
+            for (int q = 0; q < 3; ++q) ii[k][q] = in ? __ldg(&idx[3 * (size_t)pid[k] + q]) : 0;
+        }
+        float4 cr[LATE_PT][3];
+#pragma unroll
+        for (int k = 0; k < LATE_PT; ++k) {
+            if (XFORM) {
+                float ps[3][3];
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    ps[q][0] = __ldg(&xf.pos[3 * (size_t)ii[k][q]]); ps[q][1] = __ldg(&xf.pos[3 * (size_t)ii[k][q] + 1]); ps[q][2] = __ldg(&xf.pos[3 * (size_t)ii[k][q] + 2]);
+                }
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const float3 t = transform_to_screen<false>(xf.M, ps[q][0], ps[q][1], ps[q][2], xf.fw, xf.fh);
+                    cr[k][q] = make_float4(t.x, t.y, 0.0f, 0.0f);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 3; ++q) cr[k][q] = __ldg(&sv[ii[k][q]]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < LATE_PT; ++k) {
+            const int p = pid[k];
+            const float4 a = cr[k][0], b = cr[k][1], c = cr[k][2];
             bool surv = false, skip = false;
             if (p < bp.hi) {
-                const int i0 = idx[3 * (size_t)p], i1 = idx[3 * (size_t)p + 1], i2 = idx[3 * (size_t)p + 2];
-                float4 a, b, c;
-                if (XFORM) {
-                    auto corner = [&](int i) {
-                        const float3 t = transform_to_screen<false>(xf.M, xf.pos[3 * (size_t)i], xf.pos[3 * (size_t)i + 1], xf.pos[3 * (size_t)i + 2], xf.fw, xf.fh);
-                        return make_float4(t.x, t.y, 0.0f, 0.0f);
-                    };
-                    a = corner(i0); b = corner(i1); c = corner(i2);
-                } else {
-                    a = __ldg(&sv[i0]); b = __ldg(&sv[i1]); c = __ldg(&sv[i2]);
-                }
                 if (!(in_domain(a.x) && in_domain(a.y) && in_domain(b.x) && in_domain(b.y) && in_domain(c.x) && in_domain(c.y))) {
-                    skip = true;                                    // the reference traps here (R:251, R:271)
+                    skip = !(DEPTH && bp.zpass == 2);               // the reference traps here (R:251, R:271); counted once per frame
                 } else {
                     // truncation is monotone, so the sorted corners' rows s0.y / s2.y (R:271) are the min / max of the
                     // truncated rows: the clipped bounding box needs no sort
                     const int px0 = __float2int_rz(a.x), px1 = __float2int_rz(b.x), px2 = __float2int_rz(c.x);
-                    const int py0 = __float2int_rz(a.y) - fp.y_org, py1 = __float2int_rz(b.y) - fp.y_org, py2 = __float2int_rz(c.y) - fp.y_org;
-                    const int ya = max(min(py0, min(py1, py2)), 0), yb = min(max(py0, max(py1, py2)), fp.height - 1);
+                    const int qy0 = __float2int_rz(a.y), qy1 = __float2int_rz(b.y), qy2 = __float2int_rz(c.y);       // frame rows
+                    const int ya = max(min(qy0, min(qy1, qy2)) - fp.y_org, 0), yb = min(max(qy0, max(qy1, qy2)) - fp.y_org, fp.height - 1);
                     const int xa = max(min(px0, min(px1, px2)), 0), xb = min(max(px0, max(px1, px2)), fp.width - 1);
                     if (ya <= yb && xa <= xb) {
                         const int ta = xa >> TILE_SHIFT, tb = xb >> TILE_SHIFT, ra = ya >> TILE_SHIFT, rb = yb >> TILE_SHIFT;
-                        surv = !late || rb - ra >= 8;               // tall footprints are tested row by row in phase 2
-                        for (int ty = ra; ty <= rb && !surv; ++ty) surv = row_has_open(fp, ty, ta, tb);
+                        if (!DEPTH) {
+                            surv = !late || rb - ra >= 8;           // tall footprints are tested row by row in phase 2
+                            for (int ty = ra; ty <= rb && !surv; ++ty) surv = row_has_open(fp, ty, ta, tb);
+                        } else {
+                            // front / back by the nearest corner (a NaN or +inf corner depth: fminf skips a NaN; all-NaN compares false: back)
+                            const float zmin = fminf(a.z, fminf(b.z, c.z));
+                            const bool front = zmin < bp.zsplit;
+                            if (bp.zpass == 1) {
+                                surv = front;
+                                int bin = __float2int_rz(fminf(fmaxf((zmin - bp.zh_lo) * bp.zh_scale, 0.0f), (float)(ZHIST_BINS - 1)));   // NaN -> 0
+                                atomicAdd(&s_hist[bin], 1u);
+                            } else if (!front) {
+                                // behind every tile it can touch?  tile_zmax is what the front pass left (it only gets nearer)
+                                unsigned tmax = 0u;
+                                if ((tb - ta + 1) * (rb - ra + 1) > 48) tmax = 0xffffffffu;
+                                else
+                                    for (int ty = ra; ty <= rb; ++ty)
+                                        for (int tx = ta; tx <= tb; ++tx) tmax = max(tmax, __ldg(&fp.tile_zmax[ty * fp.tiles_x + tx]));
+                                surv = true;
+                                // the bound is never above the nearest corner: only then is it worth its four divisions
+                                if (tmax != 0xffffffffu && zmin == zmin && depth_ord(zmin) > tmax) {
+                                    const float dlo = triangle_depth_floor(px0, qy0, px1, qy1, px2, qy2, a.z, b.z, c.z, xa, ya + fp.y_org, xb, yb + fp.y_org);
+                                    surv = !(fabsf(dlo) < __int_as_float(0x7f800000) && depth_ord(dlo) > tmax);
+                                }
+                            }
+                        }
                     }
                 }
             }
@@ -321,6 +383,8 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
         if (lane == 0 && nskip) atomicAdd(&status->domain_skipped, nskip);
         __syncthreads();
         nsurv = s_nsurv;
+        if (DEPTH && bp.zpass == 1 && threadIdx.x < ZHIST_BINS && s_hist[threadIdx.x]) atomicAdd(&status->zhist[threadIdx.x], s_hist[threadIdx.x]);
+        if (DEPTH && bp.zpass == 2 && threadIdx.x == 0 && nsurv) atomicAdd(&status->back_survivors, (unsigned)nsurv);
     }
     unsigned small_tally = 0;
     for (int lbase = 0; lbase < nsurv; lbase += SETUP_THREADS) {
@@ -383,6 +447,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
                     if (late && tile_retired(fp, x >> TILE_SHIFT, y >> TILE_SHIFT)) return;
                     const size_t o = (size_t)y * fp.width + x;
                     if (DEPTH) {
+                        if (bp.zpass == 2) tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] = fp.epoch;   // back pass: the tile is redone
                         const float d = blend3(a.z, b.z, c.z, bary_weights(bt, x, y + fp.y_org));
                         if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, (unsigned)prim));
                     } else {
@@ -462,16 +527,8 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
             cslot = 0;
             float dlo = __int_as_float(0x7fc00000), zmin = 0.0f, zmax = 0.0f;
             if (large) {
-                const BaryT bt = bary_setup(ax, ay, bx, by, cx, cy);
-                DepthSample m = depth_sample(bt, za, zb, zc, xmin, y0 + fp.y_org);
-#pragma unroll
-                for (int q = 1; q < 4; ++q) {
-                    const DepthSample t = depth_sample(bt, za, zb, zc, (q & 1) ? xmax : xmin, ((q & 2) ? y1 : y0) + fp.y_org);
-                    m.d = fminf(m.d, t.d); m.a = fmaxf(m.a, t.a); m.b = fmaxf(m.b, t.b);
-                }
                 // the better of two rigorous bounds: over the clipped bbox rectangle, over the covered pixels
-                dlo = fmaxf(depth_lower_bound(m.d, m.a, m.b, za, zb, zc), depth_triangle_bound(bt, za, zb, zc, m.a, m.b));
-                if (!(fabsf(m.d) < __int_as_float(0x7f800000) && fabsf(m.a + m.b) < __int_as_float(0x7f800000))) dlo = __int_as_float(0x7fc00000);
+                dlo = triangle_depth_floor(ax, ay, bx, by, cx, cy, za, zb, zc, xmin, y0 + fp.y_org, xmax, y1 + fp.y_org);
 #pragma unroll
                 for (int q = 0; q < NCHUNK - 1; ++q) cslot += (dlo >= fp.zthr[q]) ? 1 : 0;    // NaN: chunk 0
                 zmin = fminf(za, fminf(zb, zc)); zmax = fmaxf(za, fmaxf(zb, zc));
@@ -507,8 +564,10 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     pos[u] = 0xffffffffu;
-                    if (tx + u <= tb && !(late && tile_retired(fp, tx + u, ty)))
+                    if (tx + u <= tb && !(late && tile_retired(fp, tx + u, ty))) {
                         pos[u] = atomicAdd(&counts[seg0 + (tx + u) * NCHUNK], 1u);
+                        if (DEPTH && bp.zpass == 2) tile_done[ty * fp.tiles_x + tx + u] = fp.epoch;
+                    }
                 }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
@@ -540,6 +599,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
                 if (late && tile_retired(fp, x >> TILE_SHIFT, y >> TILE_SHIFT)) continue;
                 const size_t o = (size_t)y * fp.width + x;
                 if (DEPTH) {
+                    if (bp.zpass == 2 && (x == l || (x & (TILE - 1)) == 0)) tile_done[(y >> TILE_SHIFT) * fp.tiles_x + (x >> TILE_SHIFT)] = fp.epoch;
                     const float3 w = bary_weights(s_bt[wbase + src], x, y + fp.y_org);
                     const float d = blend3(s_z[wbase + src][0], s_z[wbase + src][1], s_z[wbase + src][2], w);
                     if (depth_can_pass(d)) atomicMin(vis64 + o, depth_key(d, t.prim));
@@ -782,6 +842,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     __shared__ unsigned s_off[NCHUNK + 1];                 // slab lists: prefix of the tile's 16 segment lengths
     __shared__ __align__(16) unsigned s_wmax[8];           // depth mode: per-warp max of the pixels' depth_ord
     __shared__ unsigned s_zord[NCHUNK];                    // depth mode: depth_ord of the chunk thresholds
+    __shared__ unsigned s_dlo[DEPTH ? TILE_BATCH : 1];     // depth mode: depth_ord of each round triangle's lower bound over this tile (0 = none)
 
     const int tid = threadIdx.x;
     const int px = tid & (TILE - 1), py = tid >> TILE_SHIFT;
@@ -928,7 +989,9 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             // a NaN sample needs an inf/NaN constant of the triangle, which makes the margin non-finite at some corner:
             // then dlo is not finite and nothing is rejected
             const float dlo = depth_lower_bound(m.d, m.a, m.b, s_z[jq][0], s_z[jq][1], s_z[jq][2]);
-            culled = fabsf(dlo) < __int_as_float(0x7f800000) && depth_ord(dlo) > zmax_u;
+            const bool bounded = fabsf(dlo) < __int_as_float(0x7f800000);
+            culled = bounded && depth_ord(dlo) > zmax_u;
+            if (j < n && row == 0) s_dlo[j] = bounded ? depth_ord(dlo) : 0u;      // phase B: a pixel already nearer than this skips the triangle
         }
         {   // phase A: (triangle j, row) -> column mask
             unsigned mask = 0;
@@ -979,6 +1042,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                     const int b = __ffs(bits) - 1;
                     bits &= bits - 1;
                     const int jj = ((b & 15) << 1) | (b >> 4);
+                    if (s_dlo[jj] > (unsigned)(k >> 32)) continue;           // every depth of this triangle in the tile is behind the pixel (strict < fails)
                     const float3 w = bary_weights(s_bt[jj], x, y + fp.y_org);
                     const float d = blend3(s_z[jj][0], s_z[jj][1], s_z[jj][2], w);
                     if (depth_can_pass(d)) k = min(k, depth_key(d, s_prim[jj]));
@@ -1021,9 +1085,19 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             atomicAdd(&status->tiles_done, 1u);
         }
     }
+    if (DEPTH && bp.zpass == 1) {
+        // front pass of a two-pass depth frame: the tile's farthest depth is what the back pass is culled against
+        __syncthreads();                                   // every warp is done reading s_wmax
+        publish_zmax();
+        __syncthreads();
+        if (tid == 0) fp.tile_zmax[tile] = read_zmax();
+    }
     if (!inside) return;
     if (!shade_now) { if (v != v_in) vis32[o] = v; return; }      // park for the next batch
-    if (DEPTH) { if (k_in != SR_KEY_EMPTY) vis64[o] = SR_KEY_EMPTY; }   // re-arm the visibility word for the next frame
+    if (DEPTH) {
+        if (bp.zpass == 1) { if (k != k_in) vis64[o] = k; }       // keys stay parked for the back pass (its k_tile re-arms them)
+        else if (k_in != SR_KEY_EMPTY) vis64[o] = SR_KEY_EMPTY;   // re-arm the visibility word for the next frame
+    }
     else       { if (v_in) vis32[o] = 0u; }
     unsigned bgra = 0u;                                  // clear colour (R:205)
     float depth = __int_as_float(0x7f800000);            // +inf (R:206)
@@ -1038,15 +1112,30 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         // persistent CTAs: a late batch that finds most tiles retired costs a few flag reads, not thousands of CTA
         // launches; the flags of a CTA's next 32 tiles are fetched by warp 0 in ONE round trip (one dependent load per
         // tile made the almost empty final batch of the 1M soup a chain of ~10 round trips: 70 % of its stall samples)
-        __shared__ unsigned s_open;
+        // (depth mode, back pass of a two-pass frame: the tiles to do are those the back pass stamped; every other tile
+        // only has its parked keys re-armed)
+        __shared__ unsigned s_open, s_clean;
         for (int g0 = blockIdx.x; g0 < fp.ntiles; g0 += 32 * (int)gridDim.x) {
             __syncthreads();                               // s_open of the previous group has been read by everyone
             if (tid < 32) {
                 const int t = g0 + tid * (int)gridDim.x;
-                const unsigned m = __ballot_sync(0xffffffffu, t < fp.ntiles && tile_done[t] != fp.epoch);   // retired by an earlier batch?
-                if (tid == 0) s_open = m;
+                const bool stamped = t < fp.ntiles && tile_done[t] == fp.epoch;
+                const unsigned m = __ballot_sync(0xffffffffu, t < fp.ntiles && (DEPTH ? stamped : !stamped));   // depth off: retired by an earlier batch?
+                const unsigned cl = __ballot_sync(0xffffffffu, DEPTH && t < fp.ntiles && !stamped);
+                if (tid == 0) { s_open = m; s_clean = cl; }
             }
             __syncthreads();
+            if (DEPTH) {
+                unsigned clean = s_clean;
+                while (clean) {
+                    const int tile = g0 + (__ffs(clean) - 1) * (int)gridDim.x;
+                    clean &= clean - 1u;
+                    int tx, ty;
+                    divmod_tiles(tile, fp.tiles_x, ty, tx);
+                    const int x = tx * TILE + px, y = ty * TILE + py;
+                    if (x < fp.width && y < fp.height) vis64[(size_t)y * fp.width + x] = SR_KEY_EMPTY;
+                }
+            }
             unsigned open_mask = s_open;
             while (open_mask) {
                 const int tile = g0 + (__ffs(open_mask) - 1) * (int)gridDim.x;

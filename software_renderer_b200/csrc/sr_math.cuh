@@ -250,4 +250,22 @@ __device__ __forceinline__ float depth_triangle_bound(const BaryT& t, float za, 
     return fminf(za, fminf(zb, zc)) - fabsf(gx) - slack - e - 1e-37f;
 }
 
+
+// Rigorous lower bound of every depth value R:257 can produce for the triangle (original corner order a, b, c, FRAME
+// coordinates) at a pixel the span rule covers inside the clipped bounding box [xmin, xmax] x [ymin, ymax] (frame
+// rows): the better of the rectangle bound and the covered-pixel bound.  NaN = "no bound" (never reject on it).
+__device__ __forceinline__ float triangle_depth_floor(int ax, int ay, int bx, int by, int cx, int cy, float za, float zb, float zc,
+                                                      int xmin, int ymin, int xmax, int ymax) {
+    const BaryT bt = bary_setup(ax, ay, bx, by, cx, cy);
+    DepthSample m = depth_sample(bt, za, zb, zc, xmin, ymin);
+#pragma unroll
+    for (int q = 1; q < 4; ++q) {
+        const DepthSample t = depth_sample(bt, za, zb, zc, (q & 1) ? xmax : xmin, (q & 2) ? ymax : ymin);
+        m.d = fminf(m.d, t.d); m.a = fmaxf(m.a, t.a); m.b = fmaxf(m.b, t.b);
+    }
+    float dlo = fmaxf(depth_lower_bound(m.d, m.a, m.b, za, zb, zc), depth_triangle_bound(bt, za, zb, zc, m.a, m.b));
+    if (!(fabsf(m.d) < __int_as_float(0x7f800000) && fabsf(m.a + m.b) < __int_as_float(0x7f800000))) dlo = __int_as_float(0x7fc00000);
+    return dlo;
+}
+
 }  // namespace sr

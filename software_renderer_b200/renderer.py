@@ -93,6 +93,7 @@ class SrStats(ctypes.Structure):
         ("primitives", ctypes.c_uint64), ("domain_skipped", ctypes.c_uint64), ("small_tris", ctypes.c_uint64),
         ("binned_tris", ctypes.c_uint64), ("tile_pairs", ctypes.c_uint64), ("bin_regrows", ctypes.c_uint64),
         ("pairs_consumed", ctypes.c_uint64), ("batches_run", ctypes.c_uint64), ("depth_culled", ctypes.c_uint64), ("nobin_reruns", ctypes.c_uint64),
+        ("depth_two_pass_frames", ctypes.c_uint64), ("back_survivors", ctypes.c_uint64),
         ("gpu_launches", ctypes.c_uint64), ("gpu_ms", ctypes.c_float),
     ]
 
