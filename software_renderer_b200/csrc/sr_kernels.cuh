@@ -839,6 +839,10 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     __shared__ double s_rcp[TILE_BATCH][3];                 // per-edge reciprocals of the current round's triangles
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
+#ifdef SR_VEC_WB
+    __shared__ __align__(16) unsigned s_outc[TILE * TILE];   // experiment: tile staged for 16-byte row-segment stores
+    __shared__ __align__(16) float s_outd[TILE * TILE];
+#endif
     __shared__ unsigned s_off[NCHUNK + 1];                 // slab lists: prefix of the tile's 16 segment lengths
     __shared__ __align__(16) unsigned s_wmax[8];           // depth mode: per-warp max of the pixels' depth_ord
     __shared__ unsigned s_zord[NCHUNK];                    // depth mode: depth_ord of the chunk thresholds
@@ -960,10 +964,12 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
             }
         }
         // per-edge reciprocals of this round's triangles: rows 0..2 of a triangle's 16 lanes compute one each
+#ifndef SR_DIV32
         if (j < n && row < 3) {
             const TriRec& t = s_rec[cur][j];
             s_rcp[j][row] = edge_rcp(row == 0 ? t.y1 - t.y0 : (row == 1 ? t.y2 - t.y1 : t.y2 - t.y0));
         }
+#endif
         if (DEPTH && j < n && row == 0) {
             const TriRec& t = s_rec[cur][j];
             int oc[6];
@@ -1000,7 +1006,11 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
                 const SortedTri s = {t.x0, t.y0, t.x1, t.y1, t.x2, t.y2};
                 if (yy >= s.y0 && yy <= s.y2 && yy < fp.height) {
                     int l, r;
+#ifdef SR_DIV32
+                    span_row_f32(s, yy, l, r);              // experiment: 32-bit float quotient + one remainder step, no per-edge reciprocals
+#else
                     span_row_rcp(s, EdgeRcp{s_rcp[j][0], s_rcp[j][1], s_rcp[j][2]}, yy, l, r);
+#endif
                     l = max(l, x_lo);
                     r = min(r, x_hi);
                     if (l <= r) mask = ((2u << (r - l)) - 1u) << (l - x_lo);
@@ -1092,6 +1102,35 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
         __syncthreads();
         if (tid == 0) fp.tile_zmax[tile] = read_zmax();
     }
+#ifdef SR_VEC_WB
+    // experiment: interior tiles are staged in shared memory and leave as 16-byte row segments
+    // (64 threads cover a plane) instead of one 4-byte store per thread and plane
+    if (!shade_now) { if (inside && v != v_in) vis32[o] = v; return; }      // block-uniform: park for the next batch
+    unsigned bgra = 0u;                                  // clear colour (R:205)
+    float depth = __int_as_float(0x7f800000);            // +inf (R:206)
+    if (inside) {
+        if (DEPTH) {
+            if (bp.zpass == 1) { if (k != k_in) vis64[o] = k; }
+            else if (k_in != SR_KEY_EMPTY) vis64[o] = SR_KEY_EMPTY;
+        } else if (v_in) vis32[o] = 0u;
+        if (DEPTH) { if (k != SR_KEY_EMPTY) shade_pixel(in, (unsigned)k, x, y + fp.y_org, true, bgra, depth); }
+        else       { if (v) shade_pixel(in, v - 1u, x, y + fp.y_org, false, bgra, depth); }
+    }
+    const bool vec = tx * TILE + TILE <= fp.width && ty * TILE + TILE <= fp.height && (fp.width & 3) == 0 &&
+                     (reinterpret_cast<uintptr_t>(color_out) & 15) == 0 && (reinterpret_cast<uintptr_t>(depth_out) & 15) == 0;
+    if (vec) {
+        s_outc[tid] = bgra;
+        s_outd[tid] = depth;
+        __syncthreads();
+        const int t2 = tid & 63, r = t2 >> 2, sg = t2 & 3;
+        const size_t off = (size_t)(ty * TILE + r) * fp.width + tx * TILE + sg * 4;
+        if (tid < 64) *reinterpret_cast<uint4*>(color_out + off) = *reinterpret_cast<const uint4*>(&s_outc[r * TILE + sg * 4]);
+        else if (tid < 128 && depth_out) *reinterpret_cast<float4*>(depth_out + off) = *reinterpret_cast<const float4*>(&s_outd[r * TILE + sg * 4]);
+    } else if (inside) {
+        color_out[o] = bgra;
+        if (depth_out) depth_out[o] = depth;
+    }
+#else
     if (!inside) return;
     if (!shade_now) { if (v != v_in) vis32[o] = v; return; }      // park for the next batch
     if (DEPTH) {
@@ -1105,6 +1144,7 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     else       { if (v) shade_pixel(in, v - 1u, x, y + fp.y_org, false, bgra, depth); }
     color_out[o] = bgra;
     if (depth_out) depth_out[o] = depth;
+#endif
     };   // do_tile
     if (!LATE) {                                            // first (or only) batch: the grid has one CTA per tile
         do_tile(blockIdx.x);

@@ -105,6 +105,42 @@ __device__ __forceinline__ int lerp_rcp(int sx, int sy, int ex, int ey, int t, d
     else q = a / (unsigned long long)((long long)ey - (long long)sy);
     return (int)((long long)sx + (num < 0 ? -(long long)q : (long long)q));
 }
+// ---- the same quotient in 32-bit float arithmetic (-DSR_DIV32 experiment) ---------------------
+// For integers 0 <= a < 2^22 and 1 <= d < 2^24:  q0 = trunc(fl(float(a) * r)) with r = rcp.approx(float(d)) is within
+// one of floor(a / d), and one remainder step makes it exact.  float(a), float(d) are exact; rcp.approx has a relative
+// error <= 2^-23 and the product rounds once more (2^-24), so |q0' - a/d| <= (a/d) * 1.5 * 2^-23 < 2^22 * 1.5 * 2^-23 =
+// 0.75 before truncation: the truncated value is floor(a/d) - 1, floor(a/d) or floor(a/d) + 1.  With rem = a - q0 * d
+// (|rem| < 2 d < 2^25, no overflow) the quotient is q0 + (rem >= d) - (rem < 0).  Anything larger takes the 64-bit
+// division, so the result is always the reference's (R:492).  tests/test_host_math.py checks the claim on the CPU for
+// every reciprocal within the stated error.
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ int lerp_f32(int sx, int sy, int ex, int ey, int t) {
+    const long long num = (long long)(ex - sx) * (long long)(t - sy);
+    const unsigned long long a = (unsigned long long)(num < 0 ? -num : num);
+    const long long dy = (long long)ey - (long long)sy;
+    unsigned long long q;
+    if (a < (1ull << 22) && dy < (1ll << 24)) {
+        const unsigned au = (unsigned)a, d = (unsigned)dy;
+        unsigned q0 = __float2uint_rz(__fmul_rn(__uint2float_rn(au), rcp_approx(__uint2float_rn(d))));
+        const int rem = (int)au - (int)(q0 * d);
+        q0 += (rem >= (int)d) ? 1u : 0u;
+        q0 -= (rem < 0) ? 1u : 0u;
+        q = q0;
+    } else {
+        q = a / (unsigned long long)dy;
+    }
+    return (int)((long long)sx + (num < 0 ? -(long long)q : (long long)q));
+}
+__device__ __forceinline__ void span_row_f32(const SortedTri& s, int t, int& l, int& r) {
+    int a, b;
+    if (t >= s.y2) a = s.x2;
+    else if (t >= s.y1) a = lerp_f32(s.x1, s.y1, s.x2, s.y2, t);
+    else a = lerp_f32(s.x0, s.y0, s.x1, s.y1, t);
+    b = (s.y2 == s.y0) ? s.x0 : lerp_f32(s.x0, s.y0, s.x2, s.y2, t);
+    l = min(a, b);
+    r = max(a, b);
+}
+
 struct EdgeRcp { double r01, r12, r02; };
 __device__ __forceinline__ void span_row_rcp(const SortedTri& s, const EdgeRcp& m, int t, int& l, int& r) {
     int a, b;

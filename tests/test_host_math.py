@@ -140,3 +140,41 @@ def test_row_has_open_bit_logic():
             got = ((~words[wa]) & M & first) != 0 or any(((~words[w]) & M) != 0 for w in range(wa + 1, wb)) \
                 or ((~words[wb]) & M & last) != 0
         assert got == (not done[txa:txb + 1].all())
+
+
+def test_float32_quotient_with_one_remainder_step_is_exact():
+    """csrc/sr_math.cuh lerp_f32 (-DSR_DIV32 experiment): for 0 <= a < 2^22, 1 <= d < 2^24 the float estimate
+    trunc(fl(float(a) * r)) is within one of floor(a / d) for EVERY r within rcp.approx's relative error 2^-23 of 1/d, and
+    one remainder step repairs it.  The host cannot reproduce the GPU's rcp.approx bit for bit, so both ends of its error
+    interval (and the exact reciprocal) are checked: any value in between gives an estimate between these."""
+    rng = np.random.default_rng(7)
+
+    def check(a, d):
+        a = np.asarray(a, np.int64)
+        d = np.asarray(d, np.int64)
+        want = a // d
+        af, df = a.astype(np.float32), d.astype(np.float32)
+        assert np.array_equal(af.astype(np.int64), a) and np.array_equal(df.astype(np.int64), d)      # both exact in float32
+        exact = 1.0 / df.astype(np.float64)
+        for scale in (1.0 - 2.0 ** -23, 1.0, 1.0 + 2.0 ** -23):
+            r = (exact * scale).astype(np.float32)
+            q0 = np.trunc((af * r).astype(np.float32)).astype(np.int64)        # one float32 product, truncated
+            assert np.abs(q0 - want).max() <= 1
+            rem = a - q0 * d
+            assert np.abs(rem).max() < 2 ** 25                                  # the 32-bit remainder cannot overflow
+            q = q0 + (rem >= d) - (rem < 0)
+            assert np.array_equal(q, want)
+
+    # exhaustive over small operands
+    aa, dd = np.meshgrid(np.arange(0, 600), np.arange(1, 300))
+    check(aa.ravel(), dd.ravel())
+    # random over the whole admitted range, and the adversarial cases: exact multiples and one below
+    d = rng.integers(1, 1 << 24, 400_000)
+    a = rng.integers(0, 1 << 22, 400_000)
+    check(a, d)
+    d = rng.integers(1, 1 << 11, 400_000)
+    k = rng.integers(0, 1 << 11, 400_000)
+    for delta in (0, -1, 1):
+        a = np.clip(k * d + delta, 0, (1 << 22) - 1)
+        check(a, d)
+    check(np.full(4096, (1 << 22) - 1), np.arange(1, 4097))                     # largest numerator

@@ -129,14 +129,32 @@ def test_config3_soup_full_1m(renderer):
     assert s["small_tris"] + s["binned_tris"] <= 1_000_000 and s["binned_tris"] > 100_000
 
 
-def test_config5_cubesphere_512_views(renderer):
+def test_config3_soup_full_1m_depth_less(renderer):
+    """BASELINE.json calls configs[2] the "depth-test stress": the full 1M-triangle soup with the test of
+    Renderer.swift:257-261 on, two consecutive frames (the second runs with the launch policies the first one set)."""
+    v, i = S.triangle_soup(1_000_000, 1920, 1080)
+    for k in (0, 1):
+        c, d, st = assert_same(renderer, v, i, S.soup_transform(k), 1920, 1080, depth_test=True)
+    assert np.isfinite(d[c[..., 3] > 0]).all()
+    assert renderer.stats()["depth_culled"] > 0
+
+
+@pytest.mark.parametrize("depth_test", [False, True])
+def test_config5_cubesphere_512_views(renderer, depth_test):
+    """configs[4]: 32 of the 4096 camera views, spread over the whole list, in one batched call."""
     v, i = S.cube_sphere(289)
-    views = S.fibonacci_views(4096)[[0, 1000, 4095]]
+    picks = sorted(set(int(x) for x in np.linspace(0, 4095, 32)))
+    views = S.fibonacci_views(4096)[picks]
     renderer.set_mesh(v, i)
-    color, depth = renderer.render_views(views, 512, 512)
-    for k in range(3):
-        rc, rc_c, rc_d, _ = O.render(v, i, views[k], 512, 512)
-        assert rc == 0 and np.array_equal(color[k], rc_c) and np.array_equal(depth[k], rc_d)
+    renderer.depth_test = depth_test
+    try:
+        color, depth = renderer.render_views(views, 512, 512)
+    finally:
+        renderer.depth_test = False
+    for k in range(len(picks)):
+        rc, rc_c, rc_d, _ = O.render(v, i, views[k], 512, 512, flags=O.DEPTH_LESS if depth_test else 0)
+        assert rc == 0 and np.array_equal(color[k], rc_c), f"view {picks[k]}"
+        assert np.array_equal(depth[k].view(np.uint32), rc_d.view(np.uint32)), f"view {picks[k]}"
 
 
 def test_config4_cubesphere_10m_4k_properties(renderer):

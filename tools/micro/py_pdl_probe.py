@@ -24,6 +24,7 @@ from software_renderer_b200 import scene as S  # noqa: E402
 
 v, i = S.triangle_soup(1_000_000, W, H)
 r = srb.CudaRenderer(0)
+r.depth_test = bool(os.environ.get("SR_PROBE_DEPTH"))      # SR_PROBE_DEPTH=1: the depth-tested mode's timeline
 r.set_mesh(v, i)
 if mode == "notorch":
     rt = ctypes.CDLL("libcudart.so")
