@@ -23,6 +23,14 @@ __device__ __forceinline__ void pdl_wait() {
     asm volatile("griddepcontrol.launch_dependents;");
 }
 
+// The span rule's quotient (R:492) in k_tile: 32-bit float estimate + one remainder step (sr_math.cuh lerp_f32), each
+// (triangle, row) lane computing its own reciprocals.  Measured against the per-edge FP64 reciprocals it replaced
+// (-DSR_DIV_FP64 brings them back): soup1m 6,170 -> 6,289 frames/s, ico80k 17,694 -> 18,379.  Not because FP64 was slow -
+// the FP64 pipe carried 2.0 % of k_tile's instructions (profiles/r02_soup1m.md) - but because the reciprocal section ran
+// divergently on three lanes of every warp each round and its results went through shared memory.
+#if !defined(SR_DIV_FP64) && !defined(SR_DIV32)
+#define SR_DIV32 1
+#endif
 constexpr int TILE = 16;             // tile edge in pixels
 constexpr int TILE_SHIFT = 4;
 constexpr int NCHUNK = 16;           // index chunks per tile list and batch (early-out granularity)
@@ -492,8 +500,12 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN 
         // reciprocals only for binned triangles (used many times); the few rows of a small one mostly hit the
         // division-free shortcuts of span_row
         if (large && binning)
+#ifdef SR_DIV32_SETUP
+            s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0, 0.0, 0.0, 0.0, perm, 0u};
+#else
             s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0,
                                            edge_rcp(s.y1 - s.y0), edge_rcp(s.y2 - s.y1), edge_rcp(s.y2 - s.y0), perm, 0u};
+#endif
         else if (small)
             s_tri[threadIdx.x] = StagedTri{s.x0, s.y0, s.x1, s.y1, s.x2, s.y2, (unsigned)prim, y0, 0.0, 0.0, 0.0, perm, 0u};
         __syncwarp();
@@ -836,7 +848,9 @@ __global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FramePar
     __shared__ __align__(16) unsigned short s_mask[TILE][TILE_BATCH];
     __shared__ unsigned s_prim[TILE_BATCH];
     __shared__ TriRec s_rec[2][TILE_BATCH];
-    __shared__ double s_rcp[TILE_BATCH][3];                 // per-edge reciprocals of the current round's triangles
+#ifndef SR_DIV32
+    __shared__ double s_rcp[TILE_BATCH][3];                 // per-edge reciprocals of the current round's triangles (-DSR_DIV_FP64)
+#endif
     __shared__ BaryT s_bt[DEPTH ? TILE_BATCH : 1];
     __shared__ float s_z[DEPTH ? TILE_BATCH : 1][3];
 #ifdef SR_VEC_WB

@@ -160,8 +160,13 @@ __device__ __forceinline__ void span_row_rcp(const SortedTri& s, const EdgeRcp& 
 // a rectangle that holds a covered pixel; it may keep one that holds none (the two extremes can sit on different rows).
 __device__ __forceinline__ void row_band_extent(const SortedTri& s, const EdgeRcp& m, int ya, int yb, int& mn, int& mx) {
     int l0, r0, l1, r1;
+#ifdef SR_DIV32_SETUP
+    span_row_f32(s, ya, l0, r0);         // experiment: the same quotient as k_tile's, no per-edge FP64 reciprocals
+    span_row_f32(s, yb, l1, r1);
+#else
     span_row_rcp(s, m, ya, l0, r0);
     span_row_rcp(s, m, yb, l1, r1);
+#endif
     mn = min(l0, l1);
     mx = max(r0, r1);
     if (s.y1 > ya && s.y1 <= yb) { mn = min(mn, s.x1); mx = max(mx, s.x1); }  // left chain at / towards its corner row
