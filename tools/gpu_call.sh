@@ -1,18 +1,23 @@
 #!/bin/bash
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/c13_pytest.log 2>&1; tail -3 gpurun_out/c13_pytest.log
-for v in DIV32 VEC_WB; do SR_LIB=scratch/libsr_cuda_$v.so python -m pytest tests -m gpu -x -q -k "parity or fuzz or golden or bands" > gpurun_out/c13_pytest_$v.log 2>&1; echo "$v: $(tail -1 gpurun_out/c13_pytest_$v.log)"; done
-for w in soup1m ico80k cs10m4k; do
-  python bench.py --workload $w --steps 100 --warmup 20 --quick 1 > gpurun_out/c13_ab_base_$w.json 2>/dev/null
-  for v in DIV32 VEC_WB; do SR_LIB=scratch/libsr_cuda_$v.so python bench.py --workload $w --steps 100 --warmup 20 --quick 1 > gpurun_out/c13_ab_${v}_$w.json 2>/dev/null; done
-done
-python bench.py --workload soup1m --steps 100 --warmup 20 --quick 1 > gpurun_out/c13_ab_base2_soup1m.json 2>/dev/null
-python profiles/show.py gpurun_out/c13_ab_*.json | grep -v stats
-PIPES=sm__inst_executed_pipe_fp64.sum,sm__inst_executed_pipe_alu.sum,sm__inst_executed_pipe_fma.sum,sm__inst_executed_pipe_fmaheavy.sum,sm__inst_executed_pipe_lsu.sum,sm__inst_executed_pipe_xu.sum,sm__inst_executed.avg.per_cycle_active,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__inst_executed.sum,smsp__inst_executed.sum
-python bench.py --steps 2 --warmup 3 --quick 1 > gpurun_out/c13_plain.log 2>&1 &&
-ncu --set full --metrics $PIPES --clock-control none --import-source on -k regex:'k_setup|k_tile|k_transform' -s 11 -c 4 -f -o gpurun_out/r02_full_soup1m python bench.py --steps 2 --warmup 3 --quick 1 > gpurun_out/c13_ncu.log 2>&1
-python bench.py --steps 2 --warmup 3 --quick 1 > gpurun_out/c13_plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_launches_soup1m.csv python bench.py --steps 2 --warmup 3 --quick 1 > /dev/null 2>&1
-python bench.py --steps 2 --warmup 3 --quick 1 --depth-test 1 > gpurun_out/c13_plain_d.log 2>&1 &&
-ncu --set full --metrics $PIPES --clock-control none --import-source on -k regex:'k_setup|k_tile|k_transform' -s 9 -c 3 -f -o gpurun_out/r02_full_soup1m_depth python bench.py --steps 2 --warmup 3 --quick 1 --depth-test 1 > gpurun_out/c13_ncu_d.log 2>&1
-ls -la gpurun_out | grep r02_
+nvidia-smi -L | wc -l
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 8 --steps 100 --warmup 20 > gpurun_out/r02_bench_8gpu.json 2> gpurun_out/r02_bench_8gpu.err; echo "rc $?"
+python - <<'PY'
+import json
+txt = open('gpurun_out/r02_bench_8gpu.json').read()
+print('stdout lines:', len(txt.strip().splitlines()))
+d = json.loads([l for l in txt.splitlines() if l.startswith('{')][-1])
+print('value', round(d['value']), 'ms', d['ms_per_step'], 'n', d['n_gpus'])
+for k, x in d['e2e'].items():
+    if k != 'api': print('  e2e', k, x if not isinstance(x, dict) else {a: b for a, b in x.items() if a != 'api'})
+c = d['cfg5_views512']; g = c['gathered']
+print('  cfg5 views/s', round(c['value']), 'ms', c['ms_total'], '| gathered', round(g['value']), 'ms', g['ms_total'], 'overhead', g['gather_overhead_ms'], 'GB into rank0', g['bytes_into_rank0'] / 1e9, 'GB/s whole run', g['ingest_gbs_over_whole_run'], 'parity', g['composite_parity_vs_oracle_32_views'])
+PY
+python tools/pcie_probe.py --sweep 1,2,4,8 > gpurun_out/r02_pcie_probe.jsonl 2>/dev/null
+python - <<'PY'
+import json
+for l in open('gpurun_out/r02_pcie_probe.jsonl'):
+    d = json.loads(l)
+    if 'pinned' in d: print(d['n_gpus'], d['block_bytes'], 'D2H pinned agg', d['pinned']['gbs_aggregate'], 'per', d['pinned']['gbs_per_gpu'][:2], '| pageable agg', d['pageable']['gbs_aggregate'], '| H2D agg', d['h2d_pinned']['gbs_aggregate'])
+PY
+tail -2 gpurun_out/r02_bench_8gpu.err
