@@ -26,8 +26,24 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed to stdout by default) goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
+
+class OneLineStdout:
+    """stdout carries exactly ONE JSON line.  Libraries print there from C code (NCCL's "NCCL version ..." banner ignores
+    NCCL_DEBUG_FILE): for the duration of the run file descriptor 1 points at stderr, and emit() writes the line to the
+    descriptor that was stdout."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self.real = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, line: str):
+        sys.stdout.flush()
+        os.write(self.real, (line + "\n").encode())
+
+
+OUT = None
 
 WORKLOADS = {
     # name: (description, width, height)
@@ -192,7 +208,7 @@ def run_reference(args):
         "gpu_launches": 0,
         "note": "reference is Swift (no toolchain here): oracle/ C++ restatement of Renderer.swift, -O2 -ffp-contract=off",
     }
-    print(json.dumps(line), flush=True)
+    OUT.emit(json.dumps(line))
 
 
 def workload_config(desc, W, H, ntris, nverts, depth_test):
@@ -341,7 +357,7 @@ def e2e_suite(r, local, world, dev, v, i, xf, W, H, K, Wm, frame0, full: bool):
         r.depth_untouched = False
     out["no_depth_out"] = {"value": batch_leg(r, bc, None)[0], "unit": "frames/s", "api": "same, SR_FLAG_NO_DEPTH_OUT (colour only)"}
     # bare copies of the same bytes on every rank at once: what this box can deliver (the e2e roofline)
-    out["pcie_probe"] = pcie_probe(e, local, dev, W, H, bc, bd)
+    out["pcie_probe"] = pcie_probe(e, local, dev, W, H, bc, bd, r)
     if not full:
         return out
     if not depth_mode:
@@ -387,9 +403,11 @@ def e2e_suite(r, local, world, dev, v, i, xf, W, H, K, Wm, frame0, full: bool):
     return out
 
 
-def pcie_probe(e, local, dev, W, H, bc, bd):
+def pcie_probe(e, local, dev, W, H, bc, bd, r):
     """Bare cudaMemcpyAsync D2H of one frame's colour plane (and colour + depth) into the same page-locked images, all ranks at
-    once: GB/s per GPU and the frames/s that bandwidth allows.  No kernel of this repo runs."""
+    once: GB/s per GPU and the frames/s that bandwidth allows.  No kernel of this repo runs.  `colour_plus_host_fill` is the
+    ceiling of the DEFAULT e2e contract with the depth test off: the colour plane crosses PCIe while the library's host
+    threads write the +inf depth plane (sr_host_fill_depth) - 8 bytes per pixel of fresh data land in host memory per frame."""
     import torch
     src = torch.empty(8 * W * H, dtype=torch.uint8, device=dev)
     dst_c = torch.from_numpy(bc.reshape(-1))
@@ -409,6 +427,17 @@ def pcie_probe(e, local, dev, W, H, bc, bd):
                 st.synchronize()
         fps, _ = e.timed(one, n)
         res[name] = {"frames_per_s": fps, "gbs_aggregate": fps * planes * 4 * W * H / 1e9}
+
+    def fill_one():
+        n = 64
+        with torch.cuda.stream(st):
+            for k in range(n):
+                o = (k % 16) * 4 * W * H
+                dst_c[o:o + 4 * W * H].copy_(src[:4 * W * H], non_blocking=True)
+                r.host_fill_depth(bd[k % 16])
+            st.synchronize()
+    fps, _ = e.timed(fill_one, 64)
+    res["colour_plus_host_fill"] = {"frames_per_s": fps, "host_bytes_written_gbs": fps * 8 * W * H / 1e9}
     return res
 
 
@@ -480,7 +509,9 @@ def cfg5_leg(local, rank, world, dev, nviews=4096, per_rank_chunk=128):
         full_c = torch.empty((nviews, H, W, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
         full_d = torch.empty((nviews, H, W), dtype=torch.float32, device=dev) if rank == 0 else None
 
-        def run(gather: bool):
+        inf_plane = float("inf")
+
+        def run(gather: bool, render: bool = True):
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize(dev)
             if world > 1:
@@ -494,15 +525,17 @@ def cfg5_leg(local, rank, world, dev, nviews=4096, per_rank_chunk=128):
                     if gather:
                         r.gather_fence(2 * b, stream.cuda_stream)        # the gathers that read this buffer pair two chunks ago
                         r.gather_fence(2 * b + 1, stream.cuda_stream)
-                    if hi > lo:
-                        r.render_device(views[base + lo:base + hi], W, H, color[b].data_ptr(), depth[b].data_ptr(),
+                    if hi > lo and render:
+                        # depth test off: the depth plane of every view is the constant +inf (Renderer.swift:206, the test is
+                        # commented out): it is neither produced nor sent; rank 0 fills the composite's planes itself
+                        r.render_device(views[base + lo:base + hi], W, H, color[b].data_ptr(), None,
                                         stream=stream.cuda_stream, sync=False)
                     if gather and world > 1:
                         gather_views(r, color[b][:hi - lo], n_all, full_c[base:base + n_all] if rank == 0 else None, slot=2 * b, stream=stream.cuda_stream)
-                        gather_views(r, depth[b][:hi - lo], n_all, full_d[base:base + n_all] if rank == 0 else None, slot=2 * b + 1, stream=stream.cuda_stream)
                     elif gather:                                         # one GPU: the "composite" is a device copy
                         full_c[base:base + n_all].copy_(color[b][:n_all], non_blocking=True)
-                        full_d[base:base + n_all].copy_(depth[b][:n_all], non_blocking=True)
+                    if gather and rank == 0:
+                        full_d[base:base + n_all].fill_(inf_plane)
                 if gather:
                     for slot in range(4):
                         r.gather_fence(slot, stream.cuda_stream)
@@ -527,9 +560,12 @@ def cfg5_leg(local, rank, world, dev, nviews=4096, per_rank_chunk=128):
                 rc, oc, od, _ = O.render(v, i, views[k], W, H)
                 parity &= bool(rc == 0 and np.array_equal(full_c[k].cpu().numpy(), oc) and
                                np.array_equal(full_d[k].cpu().numpy().view(np.uint32), od.view(np.uint32)))
+        # the gather alone (nothing rendered: the chunk buffers are sent as they are, so this runs AFTER the parity check - it
+        # overwrites the composite with stale chunks): what NVLink + NCCL deliver into rank 0 for this message pattern
+        ms_gather_only = min(run(True, render=False), run(True, render=False)) if world > 1 else 0.0
         if world > 1:
             r.comm_destroy()
-    per_view = 8 * W * H
+    per_view = 4 * W * H                                    # colour only: the depth planes are constant and filled on rank 0
     remote = per_view * (nviews - (nviews + world - 1) // world) if world > 1 else 0       # bytes that cross NVLink into rank 0
     return {"config": workload_config(desc, W, H, ntris, nverts, False), "views": nviews, "views_per_chunk_per_rank": per_rank_chunk,
             "value": nviews / (ms_render / 1000.0), "unit": "views/s", "ms_total": ms_render,
@@ -538,7 +574,10 @@ def cfg5_leg(local, rank, world, dev, nviews=4096, per_rank_chunk=128):
                          "gather_overhead_ms": ms_gather - ms_render, "bytes_into_rank0": remote,
                          "ingest_gbs_if_unhidden": (remote / 1e9) / max((ms_gather - ms_render) / 1000.0, 1e-9) if world > 1 and ms_gather > ms_render else None,
                          "ingest_gbs_over_whole_run": (remote / 1e9) / (ms_gather / 1000.0),
-                         "api": "sr_gather (grouped ncclSend/ncclRecv on the context's gather stream), chunk k gathered while chunk k+1 renders",
+                         "gather_only_ms": ms_gather_only,
+                         "gather_only_ingest_gbs": (remote / 1e9) / (ms_gather_only / 1000.0) if ms_gather_only else None,
+                         "api": "sr_gather (grouped ncclSend/ncclRecv on the context's gather stream) of the colour images, chunk k gathered while "
+                                "chunk k+1 renders; the depth planes (depth test off: constant +inf) are filled on rank 0, not sent",
                          "composite_parity_vs_oracle_32_views": parity}}
 
 
@@ -638,7 +677,7 @@ def run_cuda(args):
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line), flush=True)
+        OUT.emit(json.dumps(line))
 
 
 def run_split(args):
@@ -736,7 +775,7 @@ def run_split(args):
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line), flush=True)
+        OUT.emit(json.dumps(line))
 
 
 def main():
@@ -751,6 +790,8 @@ def main():
     ap.add_argument("--quick", type=int, default=0, help="1: main line only (no e2e variants, no other workloads, no cfg5 leg): for kernel A/B runs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
+    global OUT
+    OUT = OneLineStdout()
     if args.impl == "reference":
         run_reference(args)
     elif args.split_frame:

@@ -114,6 +114,10 @@ int sr_host_alloc(sr_ctx* ctx, size_t bytes, void** out);
 int sr_host_free(sr_ctx* ctx, void* ptr);
 int sr_host_register(sr_ctx* ctx, void* ptr, size_t bytes);
 int sr_host_unregister(sr_ctx* ctx, void* ptr);
+/* clear(image: depthBuffer, with: .infinity) (R:206, R:232-236) on caller memory, by the context's host threads with
+ * streaming stores: `count` floats become +inf.  What the host-pointer calls do for the depth image of a pass that never
+ * tests depth; exported so that a caller can clear an image itself (and bench.py can probe the box's ceiling for it). */
+int sr_host_fill_depth(sr_ctx* ctx, float* depth, size_t count);
 
 /* -- render ---------------------------------------------------------------------------------------------------- */
 /* render(renderPass:) R:204-230 on the uploaded mesh: synchronous, writes host memory the caller owns

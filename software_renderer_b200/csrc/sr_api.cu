@@ -957,6 +957,15 @@ int sr_host_register(sr_ctx* c, void* ptr, size_t bytes) {
     return SR_OK;
 }
 
+int sr_host_fill_depth(sr_ctx* c, float* depth, size_t count) {
+    if (!c || (!depth && count)) return SR_ERR_ARG;
+    if (count == 0) return SR_OK;
+    c->pool->start(HostPool::FILL_INF, depth, nullptr, count * sizeof(float));
+    c->pool->wait();
+    if (c->last_depth_ptr == depth) c->last_depth_cleared = false;     // not this library's render call: SR_FLAG_DEPTH_UNTOUCHED starts over
+    return SR_OK;
+}
+
 int sr_host_unregister(sr_ctx* c, void* ptr) {
     if (!c || !ptr) return SR_ERR_ARG;
     SR_CUDA(c, cudaHostUnregister(ptr));

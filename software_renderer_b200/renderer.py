@@ -32,7 +32,7 @@ ABI_SYMBOLS = (
     "sr_version", "sr_create", "sr_destroy", "sr_last_error", "sr_set_mesh", "sr_render", "sr_render_pass",
     "sr_render_batch", "sr_render_device", "sr_sync", "sr_get_stats", "sr_get_kernel_times", "sr_set_profiling",
     "sr_draw2d", "sr_set_band", "sr_mesh_generation", "sr_host_alloc", "sr_host_free", "sr_host_register",
-    "sr_host_unregister", "sr_comm_unique_id", "sr_comm_init", "sr_comm_destroy", "sr_gather", "sr_gather_fence",
+    "sr_host_unregister", "sr_host_fill_depth", "sr_comm_unique_id", "sr_comm_init", "sr_comm_destroy", "sr_gather", "sr_gather_fence",
     "sr_gather_sync",
 )
 
@@ -166,6 +166,8 @@ def load_library(simd_fma: bool = False):
     L.sr_host_register.argtypes = [vp, vp, sz]
     L.sr_host_unregister.restype = i32
     L.sr_host_unregister.argtypes = [vp, vp]
+    L.sr_host_fill_depth.restype = i32
+    L.sr_host_fill_depth.argtypes = [vp, vp, sz]
     L.sr_comm_unique_id.restype = i32
     L.sr_comm_unique_id.argtypes = [vp]
     L.sr_comm_init.restype = i32
@@ -288,6 +290,11 @@ class CudaRenderer:
     def host_register(self, array: np.ndarray):
         """Page-locks memory the caller already owns (sr_host_register); undo with host_unregister."""
         self._check(self._lib.sr_host_register(self._ctx, array.ctypes.data, array.nbytes))
+
+    def host_fill_depth(self, array: np.ndarray):
+        """clear(image:with: .infinity) (Renderer.swift:206) on a float32 host array, by the library's host threads."""
+        assert array.dtype == np.float32 and array.flags.c_contiguous
+        self._check(self._lib.sr_host_fill_depth(self._ctx, array.ctypes.data, array.size))
 
     def host_unregister(self, array: np.ndarray):
         self._check(self._lib.sr_host_unregister(self._ctx, array.ctypes.data))

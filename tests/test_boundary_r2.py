@@ -182,3 +182,14 @@ def test_gather_without_a_communicator_is_an_error(renderer):
     sizes = (ctypes.c_size_t * 1)(16)
     rc = renderer._lib.sr_gather(renderer._ctx, None, None, sizes, 0, 0, None)
     assert rc == srb.renderer.SR_ERR_COMM
+
+
+def test_host_fill_depth_any_alignment_and_size(renderer):
+    """sr_host_fill_depth = clear(image: depthBuffer, with: .infinity) (Renderer.swift:206) on caller memory: the
+    streaming-store loop has an unaligned head, 64-byte thread slices and a tail."""
+    base = np.full(300_007, -2.0, np.float32)
+    for off, n in ((0, 300_007), (1, 1), (3, 17), (5, 100_003), (2, 65_536), (7, 0)):
+        base[:] = -2.0
+        renderer.host_fill_depth(base[off:off + n])
+        assert np.isposinf(base[off:off + n]).all()
+        assert (base[:off] == -2.0).all() and (base[off + n:] == -2.0).all()       # nothing outside the range is touched
