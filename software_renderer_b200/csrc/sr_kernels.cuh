@@ -49,6 +49,13 @@ constexpr int ZHIST_BINS = 64;
 #ifndef SR_SETUP_MINB
 #define SR_SETUP_MINB (5 * 256 / SR_SETUP_THREADS)
 #endif       // resident CTAs per SM asked of the binning k_setup variants (1280 threads: 47-48 registers)
+#ifndef SR_SETUP_DEPTH_MINB
+#define SR_SETUP_DEPTH_MINB SR_SETUP_MINB
+#endif       // resident CTAs per SM asked of the depth-mode k_setup variants
+#ifndef SR_TILE_DEPTH_MINB
+#define SR_TILE_DEPTH_MINB 6
+#endif       // resident CTAs per SM asked of the depth-mode k_tile.  Measured (soup1m / ico80k depth-LESS frames/s): 4 CTAs (64
+             // registers) 2,168 / 9,550; 5 (48 registers, no spill) 2,262 / 10,139; 6 (40 registers, 40 B spill) 2,321 / 10,490
 constexpr int SETUP_THREADS = SR_SETUP_THREADS;
 #ifndef SR_LATE_PT
 #define SR_LATE_PT 2
@@ -272,7 +279,7 @@ struct XformIn {
 // the list with dense warps.  Without it every warp that holds ONE survivor walks the whole binning path with 31 idle
 // lanes (48 % of the warps at a 2 % survival rate).  Results are identical: visibility is max(index), list order free.
 template <bool DEPTH, bool BIN, bool XFORM, bool COMPACT = false>
-__global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : ((BIN || DEPTH) ? SR_SETUP_MINB : 2048 / SETUP_THREADS)) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
+__global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH ? SR_SETUP_DEPTH_MINB : (BIN ? SR_SETUP_MINB : 2048 / SETUP_THREADS))) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
                                                unsigned* __restrict__ counts, TriRec* __restrict__ slab,
@@ -837,7 +844,7 @@ __device__ __forceinline__ void shade_pixel(const ShadeIn& in, unsigned prim, in
 }
 
 template <bool DEPTH, bool LATE>          // LATE: a later batch of a batched frame (persistent grid, retired tiles are skipped)
-__global__ void __launch_bounds__(256, DEPTH ? 4 : SR_TILE_MINB) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
+__global__ void __launch_bounds__(256, DEPTH ? SR_TILE_DEPTH_MINB : SR_TILE_MINB) k_tile(FrameParams fp, BatchParams bp, ShadeIn in, const TriRec* __restrict__ recs,
                                               const unsigned* __restrict__ cursor, unsigned* __restrict__ counts,
                                               const unsigned* __restrict__ pairs, unsigned* __restrict__ vis32, unsigned long long* __restrict__ vis64,
                                               unsigned* __restrict__ tile_done, ViewStatus* __restrict__ status,

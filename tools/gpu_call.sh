@@ -1,16 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-N=$(nvidia-smi -L | wc -l)
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 100 --warmup 20 > gpurun_out/r02_bench_${N}gpu.json 2> gpurun_out/r02_bench_${N}gpu.err; echo "rc $?"
-python - <<PY
-import json
-txt = open('gpurun_out/r02_bench_${N}gpu.json').read()
-print('stdout lines:', len(txt.strip().splitlines()))
-d = json.loads(txt.strip().splitlines()[-1])
-print('value', round(d['value']), 'ms', d['ms_per_step'], 'n', d['n_gpus'])
-for k, x in d['e2e'].items():
-    if k != 'api': print('  e2e', k, x if not isinstance(x, dict) else {a: b for a, b in x.items() if a != 'api'})
-c = d['cfg5_views512']; g = c['gathered']
-print('  cfg5 views/s', round(c['value']), 'ms', c['ms_total'], '| gathered', round(g['value']), 'ms', g['ms_total'], 'overhead', g['gather_overhead_ms'], 'GB into rank0', g['bytes_into_rank0'] / 1e9, 'gather-only ms', g['gather_only_ms'], 'GB/s', g['gather_only_ingest_gbs'], 'parity', g['composite_parity_vs_oracle_32_views'])
-PY
-tail -2 gpurun_out/r02_bench_${N}gpu.err
+python -m pytest tests/test_boundary_r2.py -m gpu -x -q 2>&1 | tail -2
+for v in dm5 dm6; do SR_LIB=scratch/libsr_cuda_$v.so python -m pytest tests -m gpu -x -q -k "depth or fuzz or parity" > gpurun_out/c17_pytest_$v.log 2>&1; echo "$v: $(tail -1 gpurun_out/c17_pytest_$v.log)"; done
+for rep in 1 2; do for v in base dm5 dm6; do L=""; [ $v != base ] && L=scratch/libsr_cuda_$v.so; SR_LIB=$L python bench.py --steps 50 --warmup 20 --quick 1 --depth-test 1 > gpurun_out/c17_depth_${v}_$rep.json 2>/dev/null; done; done
+for v in base dm5 dm6; do L=""; [ $v != base ] && L=scratch/libsr_cuda_$v.so; SR_LIB=$L python bench.py --workload ico80k --steps 50 --warmup 20 --quick 1 --depth-test 1 > gpurun_out/c17_icodepth_$v.json 2>/dev/null; done
+python profiles/show.py gpurun_out/c17_*.json | grep -v stats
