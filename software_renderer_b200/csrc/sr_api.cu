@@ -721,6 +721,12 @@ void print_timeline(const sr_ctx* c, size_t nviews) {
                 fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
                         (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
         fprintf(stderr, "\n");
+        static const char* ph[4] = {"classified", "staged", "binned", "small done"};
+        for (int b = 0; b < 2; ++b)
+            for (int k = 0; k < 4; ++k)
+                if (s.ph_cnt[b][k])
+                    fprintf(stderr, "  k_setup %s batch, warp reaches '%s': mean %.1f us, max %.1f us (%u warps)\n", b ? "later" : "first", ph[k],
+                            (double)s.ph_sum[b][k] / s.ph_cnt[b][k] * 1e-3, (double)s.ph_max[b][k] * 1e-3, s.ph_cnt[b][k]);
     }
 #else
     (void)c; (void)nviews;

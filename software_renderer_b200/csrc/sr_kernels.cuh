@@ -88,6 +88,10 @@ struct ViewStatus {
     // debug build: %globaltimer stamps per launch slot (2 * batch + {0 k_setup, 1 k_tile}): first CTA started,
     // first CTA past the grid dependency, last CTA finished.  Gives the overlapped timeline of a frame.
     unsigned long long tl_launch_inv[2 * MAX_BATCHES], tl_go_inv[2 * MAX_BATCHES], tl_end[2 * MAX_BATCHES];
+    // per-warp phase times of k_setup (ns since the warp passed the grid dependency), first and later batches:
+    // [batch > 0][phase]: 0 corners loaded + classified, 1 staged, 2 binned (large triangles appended), 3 small triangles rastered
+    unsigned long long ph_sum[2][4], ph_max[2][4];
+    unsigned ph_cnt[2][4];
 #endif
 };
 #ifdef SR_TIMELINE
@@ -95,10 +99,12 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 #define TL_BEGIN(st, slot) do { if (threadIdx.x == 0) atomicMax(&(st)->tl_launch_inv[slot], ~gtime()); } while (0)
 #define TL_GO(st, slot)    do { if (threadIdx.x == 0) atomicMax(&(st)->tl_go_inv[slot], ~gtime()); } while (0)
 #define TL_END(st, slot)   do { if ((threadIdx.x & 31) == 0) atomicMax(&(st)->tl_end[slot], gtime()); } while (0)   /* every warp: thread 0 may finish long before its CTA */
+#define TL_PHASE(st, b, k, t0) do { if ((threadIdx.x & 31) == 0) { const unsigned long long d__ = gtime() - (t0); atomicAdd(&(st)->ph_sum[b][k], d__); atomicMax(&(st)->ph_max[b][k], d__); atomicAdd(&(st)->ph_cnt[b][k], 1u); } } while (0)
 #else
 #define TL_BEGIN(st, slot) do {} while (0)
 #define TL_GO(st, slot)    do {} while (0)
 #define TL_END(st, slot)   do {} while (0)
+#define TL_PHASE(st, b, k, t0) do {} while (0)
 #endif
 
 // Bin-list record of a large triangle (32 B = one sector): corners SORTED as R:271 leaves them and the sort
@@ -287,6 +293,10 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
     TL_BEGIN(status, 2 * bp.index);
     pdl_wait();
     TL_GO(status, 2 * bp.index);
+#ifdef SR_TIMELINE
+    const unsigned long long tl_t0 = gtime();
+    const int tl_b = bp.index > 0 ? 1 : 0;
+#endif
     __shared__ StagedTri s_tri[SETUP_THREADS];
     __shared__ StagedRect s_rect[BIN ? SETUP_THREADS : 1];
     __shared__ BaryT s_bt[DEPTH ? SETUP_THREADS : 1];
@@ -492,6 +502,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
         sv[i1] = make_float4(fx[1], fy[1], 0.0f, 0.0f);
         sv[i2] = make_float4(fx[2], fy[2], 0.0f, 0.0f);
     }
+    TL_PHASE(status, tl_b, 0, tl_t0);
     // warp-aggregated counters and bin-list append
     const unsigned m_skip = __ballot_sync(0xffffffffu, skipped);
     const unsigned m_small = __ballot_sync(0xffffffffu, small);
@@ -531,6 +542,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
         ta = max(ta, mn >> TILE_SHIFT);
         tb = min(tb, mx >> TILE_SHIFT);
     };
+    TL_PHASE(status, tl_b, 1, tl_t0);
     if (binning) {
         // compact lists: records are compacted into `recs`, the lists hold their slots; slab lists hold records
         unsigned slot = 0;
@@ -604,6 +616,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
         if (seg_max) atomicMax(&status->seg_max, seg_max);          // a segment overflowed: the host grows the slabs and re-runs
     }
 
+    TL_PHASE(status, tl_b, 2, tl_t0);
     // (b) small triangles: one item per clipped row -> global atomics on the visibility words
     if (m_small) {                                           // warp-uniform
         warp_balance(small ? (y1 - y0 + 1) : 0, [&](int src, int item) {
@@ -628,6 +641,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
             }
         });
     }
+    TL_PHASE(status, tl_b, 3, tl_t0);
     small_tally += __popc(m_small) + __popc(m_tiny);
     __syncwarp();                                            // COMPACT: the next pass reuses this warp's staging slots
     }   // survivor passes
