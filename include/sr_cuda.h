@@ -182,6 +182,34 @@ int sr_gather(sr_ctx* ctx, const void* send_dev, void* recv_dev, const size_t* b
 int sr_gather_fence(sr_ctx* ctx, int slot, void* stream);
 int sr_gather_sync(sr_ctx* ctx);
 
+/* -- allocation-free entry point ------------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * One render pass of PrimitiveType.vertices (the arithmetic of R:295-302 after the clears of R:205-206: every corner
+ * plots one pixel, the last corner in submission order wins, depth stays +inf) that allocates NOTHING: no sr_ctx, no
+ * cudaMalloc / cudaFree / cudaMallocHost, no allocating library routine.  Its per-pixel visibility words live in a
+ * file-scope `static __device__` array of SR_NOALLOC_MAX_PIXELS words (4 MiB) that every GPU which loads this library
+ * holds until the process exits.  Inputs and outputs are the caller's DEVICE memory:
+ *   vertices_dev   nverts Swift-layout vertices (sr_vertex, 32 bytes), 16-byte aligned
+ *   indices_dev    nidx Swift `Int` indices (int64); corners used = (nidx / 3) * 3, as R:221; an index outside
+ *                  [0, nverts) makes that corner plot nothing (the reference traps at R:226; checking the whole array
+ *                  first would need a host round trip and scratch of its own)
+ *   transform_colmajor16   HOST memory, 16 floats, passed to the kernel by value
+ *   color_bgra_dev width*height*4 bytes; depth_dev width*height floats or NULL
+ *   cuda_stream    a cudaStream_t, NULL = the default stream.  The call only enqueues: it returns without waiting.
+ * Returns SR_ERR_ARG when width * height > SR_NOALLOC_MAX_PIXELS (or on null / non-positive arguments), SR_ERR_CUDA
+ * on a CUDA failure, else SR_OK.  Corners outside the valid domain are skipped but NOT counted (no status word).
+ * SHARED STATE: every call on a GPU uses the same array, which keeps its contents between calls; each call leaves it
+ * all zero again (the resolve kernel re-arms every word it reads) and the first call on a device clears it.  Calls that
+ * overlap on one GPU (two streams, two threads) RACE on it: serialise them.  sr_points_no_alloc_last_error() returns a
+ * static string describing the last failure of this entry point in the calling process. */
+#define SR_NOALLOC_MAX_PIXELS (1u << 20)
+int sr_points_no_alloc(int device, const sr_vertex* vertices_dev, size_t nverts, const int64_t* indices_dev, size_t nidx,
+                       const float* transform_colmajor16, int width, int height, void* color_bgra_dev, void* depth_dev,
+                       void* cuda_stream);
+const char* sr_points_no_alloc_last_error(void);
+
 /* Counters of the last completed render call. */
 int sr_get_stats(sr_ctx* ctx, sr_stats* out);
 

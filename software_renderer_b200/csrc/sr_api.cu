@@ -1315,3 +1315,113 @@ int sr_get_kernel_times(sr_ctx* c, const char** names, float* ms, int cap) {
 }
 
 }  // extern "C"
+
+// =================================================================================================================
+// Allocation-free entry point (include/sr_cuda.h: sr_points_no_alloc).  No counterpart in the reference.
+// Nothing below calls cudaMalloc, cudaFree, cudaMallocHost or any allocating routine,
+// and nothing above uses any of it: no existing code path changes.
+// =================================================================================================================
+namespace {
+
+// The scratch: one visibility word per pixel (corner number + 1, 0 = background), SR_NOALLOC_MAX_PIXELS words = 4 MiB,
+// held by every GPU that loads the library until the process exits.  In HOST code this name is a host-side stand-in,
+// not a device address: kernels get the pointer cudaGetSymbolAddress returns (below), never `g_noalloc_vis` itself.
+static __device__ __align__(256) unsigned g_noalloc_vis[SR_NOALLOC_MAX_PIXELS];
+
+constexpr int kNoAllocMaxDevices = 64;
+unsigned* g_noalloc_ptr[kNoAllocMaxDevices] = {};      // per device: the array's device address, resolved once
+bool g_noalloc_ready[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+char g_noalloc_err[512] = "";
+
+__global__ void __launch_bounds__(256) k_na_clear(unsigned* __restrict__ vis, unsigned n) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) vis[i] = 0u;
+}
+
+// R:295-302 per corner, straight from the Swift-layout arrays: Vertex.apply + convertedToScreen (R:159-172, the same
+// device function the context path uses), Int(x), Int(y) truncating (R:298-299), bounds-checked store (R:30-36); the
+// last corner in submission order wins = max(corner number + 1).
+__global__ void __launch_bounds__(256) k_na_scatter(const float4* __restrict__ verts, unsigned long long nverts,
+                                                    const long long* __restrict__ idx, unsigned ncorners, Mat4 M, int W, int H,
+                                                    unsigned* __restrict__ vis) {
+    const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncorners) return;
+    const long long i = idx[c];
+    if (i < 0 || (unsigned long long)i >= nverts) return;                    // the reference traps (R:226): plots nothing here
+    const float4 p = verts[2 * (size_t)i];
+    const float3 s = transform_to_screen<false>(M, p.x, p.y, p.z, (float)W, (float)H);
+    if (!(in_domain(s.x) && in_domain(s.y))) return;                         // the reference traps (R:298)
+    const int x = __float2int_rz(s.x), y = __float2int_rz(s.y);
+    if (x >= 0 && x < W && y >= 0 && y < H) atomicMax(vis + (size_t)y * W + x, c + 1u);
+}
+
+// Clears fused into the write-back (R:205-206), Pixel(float3: vertex.color) for the winner (R:300), and every word read
+// is put back to zero, so the shared array is clean for the next call.
+__global__ void __launch_bounds__(256) k_na_resolve(const float4* __restrict__ verts, const long long* __restrict__ idx, unsigned npx,
+                                                    unsigned* __restrict__ vis, unsigned* __restrict__ color_out, float* __restrict__ depth_out) {
+    const unsigned o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= npx) return;
+    const unsigned v = vis[o];
+    unsigned bgra = 0u;
+    if (v) {
+        vis[o] = 0u;
+        const float4 col = verts[2 * (size_t)idx[v - 1u] + 1];
+        bgra = pack_bgra(col.x, col.y, col.z);
+    }
+    color_out[o] = bgra;
+    if (depth_out) depth_out[o] = __int_as_float(0x7f800000);
+}
+
+int na_fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+    if (e != cudaSuccess) snprintf(g_noalloc_err, sizeof g_noalloc_err, "sr_points_no_alloc: %s: %s", what, cudaGetErrorString(e));
+    else snprintf(g_noalloc_err, sizeof g_noalloc_err, "sr_points_no_alloc: %s", what);
+    return code;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* sr_points_no_alloc_last_error(void) { return g_noalloc_err; }
+
+int sr_points_no_alloc(int device, const sr_vertex* vertices_dev, size_t nverts, const int64_t* indices_dev, size_t nidx,
+                       const float* transform, int W, int H, void* color_dev, void* depth_dev, void* cuda_stream) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);       // host-side state only: GPU work of overlapping calls still races (header)
+    if (!transform || !color_dev || W <= 0 || H <= 0) return na_fail(SR_ERR_ARG, "null transform / colour pointer or non-positive size");
+    if ((nverts && !vertices_dev) || (nidx && !indices_dev)) return na_fail(SR_ERR_ARG, "null mesh pointer");
+    if ((unsigned long long)W * (unsigned long long)H > (unsigned long long)SR_NOALLOC_MAX_PIXELS) {
+        snprintf(g_noalloc_err, sizeof g_noalloc_err, "sr_points_no_alloc: %d x %d = %llu pixels exceed the static scratch of %u pixels "
+                 "(SR_NOALLOC_MAX_PIXELS); use sr_render* with a context for larger images", W, H, (unsigned long long)W * H, SR_NOALLOC_MAX_PIXELS);
+        return SR_ERR_ARG;
+    }
+    if (nidx / 3 * 3 > 0xFFFFFFF0ull) return na_fail(SR_ERR_ARG, "too many corners (32-bit corner numbers)");
+    if (device < 0 || device >= kNoAllocMaxDevices) return na_fail(SR_ERR_ARG, "device ordinal out of range");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return na_fail(SR_ERR_CUDA, "cudaSetDevice", e);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const unsigned npx = (unsigned)W * (unsigned)H;
+    if (!g_noalloc_ready[device]) {
+        // once per device, with that device current: the array's DEVICE address (the symbol itself is a host stand-in)
+        unsigned* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_vis);
+        if (e != cudaSuccess || !ptr) return na_fail(SR_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_vis)", e);
+        g_noalloc_ptr[device] = ptr;
+        k_na_clear<<<div_up(SR_NOALLOC_MAX_PIXELS, 256), 256, 0, st>>>(ptr, SR_NOALLOC_MAX_PIXELS);     // must start at zero
+        if ((e = cudaGetLastError()) != cudaSuccess) return na_fail(SR_ERR_CUDA, "k_na_clear launch", e);
+        g_noalloc_ready[device] = true;
+    }
+    unsigned* vis = g_noalloc_ptr[device];
+    Mat4 M;
+    std::memcpy(M.m, transform, sizeof M.m);
+    const unsigned ncorners = (unsigned)(nidx / 3 * 3);                       // R:221: a trailing partial primitive is ignored
+    if (ncorners)
+        k_na_scatter<<<div_up(ncorners, 256), 256, 0, st>>>((const float4*)vertices_dev, (unsigned long long)nverts, (const long long*)indices_dev,
+                                                            ncorners, M, W, H, vis);
+    k_na_resolve<<<div_up(npx, 256), 256, 0, st>>>((const float4*)vertices_dev, (const long long*)indices_dev, npx, vis, (unsigned*)color_dev, (float*)depth_dev);
+    if ((e = cudaGetLastError()) != cudaSuccess) return na_fail(SR_ERR_CUDA, "kernel launch", e);
+    g_noalloc_err[0] = 0;
+    return SR_OK;
+}
+
+}  // extern "C"

@@ -33,7 +33,7 @@ ABI_SYMBOLS = (
     "sr_render_batch", "sr_render_device", "sr_sync", "sr_get_stats", "sr_get_kernel_times", "sr_set_profiling",
     "sr_draw2d", "sr_set_band", "sr_mesh_generation", "sr_host_alloc", "sr_host_free", "sr_host_register",
     "sr_host_unregister", "sr_host_fill_depth", "sr_comm_unique_id", "sr_comm_init", "sr_comm_destroy", "sr_gather", "sr_gather_fence",
-    "sr_gather_sync",
+    "sr_gather_sync", "sr_points_no_alloc", "sr_points_no_alloc_last_error",
 )
 
 
@@ -168,6 +168,10 @@ def load_library(simd_fma: bool = False):
     L.sr_host_unregister.argtypes = [vp, vp]
     L.sr_host_fill_depth.restype = i32
     L.sr_host_fill_depth.argtypes = [vp, vp, sz]
+    L.sr_points_no_alloc.restype = i32
+    L.sr_points_no_alloc.argtypes = [i32, vp, sz, vp, sz, vp, i32, i32, vp, vp, vp]
+    L.sr_points_no_alloc_last_error.restype = ctypes.c_char_p
+    L.sr_points_no_alloc_last_error.argtypes = []
     L.sr_comm_unique_id.restype = i32
     L.sr_comm_unique_id.argtypes = [vp]
     L.sr_comm_init.restype = i32

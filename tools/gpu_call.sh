@@ -1,3 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for d in "" 1; do echo "== phases, depth=${d:-0}"; SR_PROBE_DEPTH=$d SR_LIB=scratch/libsr_cuda_tl.so python tools/micro/py_pdl_probe.py torch 2>&1 | grep -E "^view|k_setup" | tail -9; done
+echo "== alone, fresh process"; python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/na_alone.log 2>&1; echo "rc $?"; tail -15 gpurun_out/na_alone.log
+echo "== after the other tests (pytest -x, whole suite)"; python -m pytest tests -m gpu -x -q > gpurun_out/na_suite.log 2>&1; echo "rc $?"; tail -4 gpurun_out/na_suite.log
+python -m pytest tests -m gpu -q --collect-only 2>/dev/null | tail -4
