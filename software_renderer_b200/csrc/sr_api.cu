@@ -205,6 +205,9 @@ struct sr_ctx {
     double first_frac = 0.125;           // batched frames: share of the primitives (from the top) in the first batch
     int force_batches = -1;              // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     bool use_pdl = true;
+    int max_spread = 0;                  // SR_SPREAD: largest spread_shift the binning k_setup may use on under-filled grids (0 = off)
+    double spread_waves = 1.5;           // SR_SPREAD_WAVES: ... as long as the spread grid stays within this many waves
+    int sm_count = 148;
     bool use_compact = false;            // SR_COMPACT=1: late batches of depth-off frames run the compacting k_setup (measured: slower)
     // speculative frames without the binning kernels: enabled after a frame in which no triangle was large; a frame
     // that does meet a large triangle only counts it and is re-run with the full pipeline (results identical)
@@ -488,8 +491,8 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
         } else if (two_pass) {
             if (!c->zsplit_valid) { c->zsplit = c->zh_lo + 0.25f * (c->zh_hi - c->zh_lo); c->zsplit_valid = true; }
             const float scale = c->zh_hi > c->zh_lo ? (float)ZHIST_BINS / (c->zh_hi - c->zh_lo) : 0.0f;
-            batches[nb++] = BatchParams{0, ntris, 0, 0, 0, 1, c->zsplit, c->zh_lo, scale};
-            batches[nb++] = BatchParams{0, ntris, 0, 1, 1, 2, c->zsplit, c->zh_lo, scale};
+            batches[nb++] = BatchParams{0, ntris, 0, 0, 0, 0, 1, c->zsplit, c->zh_lo, scale};
+            batches[nb++] = BatchParams{0, ntris, 0, 1, 1, 0, 2, c->zsplit, c->zh_lo, scale};
         } else {
             batches[nb++] = BatchParams{0, ntris, 0, 0, 1};
         }
@@ -508,7 +511,13 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
                                                  : (fp.batched ? (compact ? k_setup<false, true, true, true> : k_setup<false, true, true>)
                                                                : k_setup<false, true, false>));
                 XformIn xf{c->pos.p, M, (float)W, (float)Hframe};
-                launch_pdl(c, ks, div_up(n, compact ? SETUP_THREADS * LATE_PT : SETUP_THREADS), SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
+                // an under-filled grid: fewer triangles per warp (BatchParams::spread_shift), while the grid stays within
+                // spread_waves waves of 5 CTAs per SM.  SR_SPREAD=0 (default until measured) leaves it off.
+                if (!compact && !fp.nobin && c->max_spread > 0) {
+                    const size_t one_wave = (size_t)c->sm_count * 5 * SETUP_THREADS;
+                    while (bp.spread_shift < c->max_spread && (double)((size_t)n << (bp.spread_shift + 1)) <= c->spread_waves * (double)one_wave) bp.spread_shift++;
+                }
+                launch_pdl(c, ks, div_up(compact ? (size_t)n : ((size_t)n << bp.spread_shift), compact ? SETUP_THREADS * LATE_PT : SETUP_THREADS), SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
             }
             if (!fp.nobin && !fp.slab_cap) {
@@ -817,6 +826,9 @@ int sr_create(sr_ctx** out, int device) {
         set_frame_carveouts(pct);
         cudaGetLastError();
     }
+    if (const char* e = getenv("SR_SPREAD")) c->max_spread = std::max(0, std::min(3, atoi(e)));
+    if (const char* e = getenv("SR_SPREAD_WAVES")) c->spread_waves = std::max(0.5, atof(e));
+    { int v = 0; if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && v > 0) c->sm_count = v; }
     if (const char* e = getenv("SR_ZPASS")) { c->force_zpass = atoi(e); c->depth_two_pass = c->force_zpass > 0; }
     if (const char* e = getenv("SR_ZFRAC")) c->zfrac = std::min(0.9, std::max(0.005, atof(e)));
     if (const char* e = getenv("SR_COMPACT")) c->use_compact = atoi(e) != 0;

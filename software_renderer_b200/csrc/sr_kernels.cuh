@@ -227,6 +227,12 @@ struct BatchParams {
     // whose rigorous depth lower bound is behind all the tiles of its bounding box (it cannot pass the strict < of
     // R:258 anywhere); tiles that receive anything are stamped in tile_done and redone by a persistent k_tile from the
     // parked keys.  zpass 0 = the single pass.  The image is the same in all three.
+    // Triangles per warp = 32 >> spread_shift.  A batch whose grid does not fill the GPU (the first batch of a batched
+    // frame: 125 k triangles = 26 of 64 warp slots per SM, one wave) lasts as long as ONE warp's chain of dependent work,
+    // most of it the binning rounds (32 tile-row items per round).  Spreading the triangles over 2x or 4x the warps
+    // (every 2nd / 4th lane holds a triangle) shortens that chain; the host picks the shift so that the grid still fits
+    // about one wave.  Nothing else changes: every loop below is driven by ballots and prefix sums over the live lanes.
+    int spread_shift;
     int zpass;
     float zsplit;
     float zh_lo, zh_scale;    // histogram bin of a depth z: (z - zh_lo) * zh_scale, clamped to [0, ZHIST_BINS)
@@ -414,8 +420,10 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
     unsigned small_tally = 0;
     for (int lbase = 0; lbase < nsurv; lbase += SETUP_THREADS) {
     if (COMPACT && lbase + wbase >= nsurv) break;            // warp-uniform: this warp has no survivor left
-    const bool valid = COMPACT ? (lbase + (int)threadIdx.x < nsurv) : (bp.lo + (int)(blockIdx.x * blockDim.x + threadIdx.x) < bp.hi);
-    const int prim = COMPACT ? (valid ? s_list[lbase + threadIdx.x] : 0) : bp.lo + (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    const int gtid = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    const bool holds = (threadIdx.x & ((1u << bp.spread_shift) - 1u)) == 0u;          // spread: every 2^shift-th lane holds a triangle
+    const bool valid = COMPACT ? (lbase + (int)threadIdx.x < nsurv) : (holds && bp.lo + (gtid >> bp.spread_shift) < bp.hi);
+    const int prim = COMPACT ? (valid ? s_list[lbase + threadIdx.x] : 0) : bp.lo + (gtid >> bp.spread_shift);
     bool skipped = false, tiny = false, small = false, large = false;
     SortedTri s = {};
     int ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, y0 = 0, y1 = -1, xmin = 0, xmax = -1;
