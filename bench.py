@@ -216,6 +216,9 @@ def workload_config(desc, W, H, ntris, nverts, depth_test):
     return {"workload": desc, "width": W, "height": H, "triangles": ntris, "vertices": nverts, "depth_test": bool(depth_test)}
 
 
+REGION_STATS = {}
+
+
 def device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, frame0, dev):
     """K timed frames, device resident, L2 flushed between frames; returns (per-frame ms array, launches, wall s)."""
     import torch
@@ -245,10 +248,23 @@ def device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, frame0, dev):
             frame(Wm + k)                               # asynchronous; calls accumulate, no host round trip
             evs[k][1].record(stream)
         r.sync()                                        # one status read-back for all K frames
-        launches = r.stats()["gpu_launches"]
+        ev_tail = torch.cuda.Event(enable_timing=True)
+        ev_tail.record(stream)
+        region = r.stats()                              # counters of the K timed frames (one accumulated call)
+        launches = region["gpu_launches"]
         torch.cuda.synchronize(dev)
         wall = time.perf_counter() - t0
-    return np.array([a.elapsed_time(b) for a, b in evs]), int(launches), wall
+    # frames re-run after a failed speculation (list capacity, no-binning guess) run at the sync, outside
+    # the per-frame event pairs: they are reported so that a line that lived on re-runs cannot hide it
+    REGION_STATS.clear()
+    REGION_STATS.update({k: int(region[k]) for k in ("bin_regrows", "nobin_reruns", "tile_pairs", "pairs_consumed", "depth_culled")})
+    per_frame = np.array([a.elapsed_time(b) for a, b in evs])
+    reruns = REGION_STATS["bin_regrows"] + REGION_STATS["nobin_reruns"]
+    if reruns:                                          # charge the re-runs (and the host round trip before them) to the last frame
+        torch.cuda.synchronize(dev)
+        per_frame[-1] += evs[-1][1].elapsed_time(ev_tail)
+        REGION_STATS["rerun_tail_ms_charged"] = float(evs[-1][1].elapsed_time(ev_tail))
+    return per_frame, int(launches), wall
 
 
 def kernel_split(r, xf, W, H, color, depth, stream, flush, frame0, dev, reps=5):
@@ -461,6 +477,7 @@ def workload_record(name, depth_test, local, dev, stream, flush, K=20, Wm=5):
         color = torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
         depth = torch.empty((H, W), dtype=torch.float32, device=dev)
         per_frame, launches, _ = device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, 0, dev)
+        region_stats = dict(REGION_STATS)
         acc = kernel_split(r, xf, W, H, color, depth, stream, flush, 0, dev, reps=3)
         frame_ms = float(per_frame.mean())
         CH = 8
@@ -481,7 +498,7 @@ def workload_record(name, depth_test, local, dev, stream, flush, K=20, Wm=5):
             "frame_roofline": frame_roofline_of(frame_ms, ntris, nverts, W, H),
             "roofline": roofline_of(acc, ntris, nverts, W, H, name + ("_depth" if depth_test else "")),
             "kernel_ms": acc, "e2e": {"value": e2e, "unit": "frames/s", "api": "sr_render_batch, 8 frames per call, page-locked images"},
-            "parity_vs_oracle": ok, "gpu_launches_per_frame": launches // K,
+            "parity_vs_oracle": ok, "gpu_launches_per_frame": launches // K, "timed_region_stats": region_stats,
             "stats_last_frame": {k: (int(x) if k != "gpu_ms" else float(x)) for k, x in stats.items()}}
 
 
@@ -613,6 +630,7 @@ def run_cuda(args):
     sampler = ClockSampler(local)
     sampler.start()
     per_frame, launches, t_wall = device_fps(r, xf, W, H, color, depth, stream, flush, K, Wm, frame0, dev)
+    region_stats = dict(REGION_STATS)
     if world > 1:
         dist.barrier()
     clocks = sampler.stop()
@@ -655,6 +673,7 @@ def run_cuda(args):
                                        f"frame; host has {cpu_count()} cores"},
             "e2e": e2e,
             "gpu_launches": int(launches),
+            "timed_region_stats": dict(region_stats),
             "clocks": clocks,
             "wall_s_timed_region": t_wall,
             "stats_last_frame": {k: (int(x) if k != "gpu_ms" else float(x)) for k, x in stats.items()},

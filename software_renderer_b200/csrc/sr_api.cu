@@ -205,10 +205,14 @@ struct sr_ctx {
     double first_frac = 0.125;           // batched frames: share of the primitives (from the top) in the first batch
     int force_batches = -1;              // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     bool use_pdl = true;
+    bool debug_sync = false;             // SR_DEBUG_SYNC=1: synchronise and report after every frame-kernel launch
     int max_spread = 0;                  // SR_SPREAD: largest spread_shift the binning k_setup may use on under-filled grids (0 = off)
     double spread_waves = 1.5;           // SR_SPREAD_WAVES: ... as long as the spread grid stays within this many waves
     int sm_count = 148;
     bool use_compact = false;            // SR_COMPACT=1: late batches of depth-off frames run the compacting k_setup (measured: slower)
+    bool use_lbox = true;                // SR_LBOX=0: no box pre-pass in batched frames: the later batches transform every triangle themselves
+                                         //   (the path frames with more than 255 tiles per axis take).  Measured on the 1M soup: 6,320 -> 6,657 frames/s
+    DevBuf<unsigned> lbox;               // batched frames: clipped tile bounding box per primitive of the later batches (FrameParams::lbox)
     // speculative frames without the binning kernels: enabled after a frame in which no triangle was large; a frame
     // that does meet a large triangle only counts it and is re-run with the full pipeline (results identical)
     bool nobin_mode = false, call_nobin = false, allow_nobin = true;   // SR_NOBIN=0 disables
@@ -335,6 +339,10 @@ void launch_pdl(sr_ctx* c, void (*kernel)(KArgs...), unsigned grid, unsigned blo
     cfg.attrs = attr;
     cfg.numAttrs = c->use_pdl ? 1 : 0;
     cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    if (c->debug_sync) {                  // SR_DEBUG_SYNC=1: find the launch that faults (launch ordinal of the call, grid, error)
+        const cudaError_t e = cudaStreamSynchronize(st);
+        fprintf(stderr, "[sr debug] launch %llu grid %u block %u: %s\n", (unsigned long long)c->launches, grid, block, cudaGetErrorString(e));
+    }
 }
 
 int primitive_vertices(int prim) { return prim == SR_LINE ? 2 : 3; }   // R:179-188
@@ -354,6 +362,7 @@ void set_frame_carveouts(int pct) {
     set_carveout(k_setup<false, false, false>, pct); set_carveout(k_setup<false, true, false>, pct);
     set_carveout(k_setup<false, true, true>, pct);   set_carveout(k_setup<false, true, true, true>, pct);
     set_carveout(k_setup<true, true, false, true>, pct); set_carveout(k_tile<true, true>, pct);
+    set_carveout(k_setup<false, true, true, true, true>, pct); set_carveout(k_late_boxes, pct);
     set_carveout(k_scan, pct); set_carveout(k_bin_fill, pct);
     set_carveout(k_tile<true, false>, pct); set_carveout(k_tile<false, false>, pct); set_carveout(k_tile<false, true>, pct);
     set_carveout(k_resolve<true, 1>, pct); set_carveout(k_resolve<true, 4>, pct);
@@ -391,6 +400,7 @@ int ensure_frame_buffers(sr_ctx* c, int W, int H, bool depth_mode, size_t nviews
         SR_CUDA(c, c->done_bits.reserve(nbits_words));
         SR_CUDA(c, cudaMemsetAsync(c->done_bits.p, 0, nbits_words * sizeof(unsigned), st));
     }
+    if (!depth_mode && c->batched_mode && c->use_lbox) SR_CUDA(c, c->lbox.reserve(std::max<size_t>(c->nidx / 3, 1)));
     const size_t nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
     if (nblocks > c->look.cap) {
         SR_CUDA(c, c->look.reserve(nblocks));
@@ -478,6 +488,9 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
         fp.nobin = (c->nobin_mode && c->allow_nobin && !fp.batched) ? 1 : 0;
         if (fp.nobin) c->call_nobin = true;
         fp.tile_zmax = c->tile_zmax.p;
+        // box pre-pass (FrameParams::lbox): tile coordinates must fit a byte, the buffer must hold one word per primitive
+        fp.lbox = (fp.batched && c->use_lbox && !c->use_compact && c->max_spread == 0 && fp.tiles_x <= LBOX_MAX_TILES && fp.tiles_y <= LBOX_MAX_TILES &&
+                   c->lbox.cap >= (size_t)ntris) ? c->lbox.p : nullptr;
         const bool two_pass = depth_mode && c->depth_two_pass && fp.slab_cap > 0 && !fp.nobin && ntris >= (1 << 16);
         const int ncnt = fp.ntiles * NCHUNK;
         BatchParams batches[MAX_BATCHES];
@@ -505,10 +518,11 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
                 prof_mark(c, st, "k_setup");
                 // later batches of a batched frame mostly meet retired tiles: the compacting variant (cheap test first,
                 // full setup on the survivors with dense warps)
-                const bool compact = (fp.batched && b > 0 && c->use_compact) || two_pass;
+                const bool pre = fp.lbox != nullptr && b > 0;   // later batch of a frame with the box pre-pass: starts from its words
+                const bool compact = (fp.batched && b > 0 && (c->use_compact || pre)) || two_pass;
                 auto ks = depth_mode ? (fp.nobin ? k_setup<true, false, false> : (two_pass ? k_setup<true, true, false, true> : k_setup<true, true, false>))
                                      : (fp.nobin ? k_setup<false, false, false>
-                                                 : (fp.batched ? (compact ? k_setup<false, true, true, true> : k_setup<false, true, true>)
+                                                 : (fp.batched ? (pre ? k_setup<false, true, true, true, true> : (compact ? k_setup<false, true, true, true> : k_setup<false, true, true>))
                                                                : k_setup<false, true, false>));
                 XformIn xf{c->pos.p, M, (float)W, (float)Hframe};
                 // an under-filled grid: fewer triangles per warp (BatchParams::spread_shift), while the grid stays within
@@ -517,8 +531,14 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
                     const size_t one_wave = (size_t)c->sm_count * 5 * SETUP_THREADS;
                     while (bp.spread_shift < c->max_spread && (double)((size_t)n << (bp.spread_shift + 1)) <= c->spread_waves * (double)one_wave) bp.spread_shift++;
                 }
-                launch_pdl(c, ks, div_up(compact ? (size_t)n : ((size_t)n << bp.spread_shift), compact ? SETUP_THREADS * LATE_PT : SETUP_THREADS), SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
+                const unsigned sgrid = div_up(compact ? (size_t)n : ((size_t)n << bp.spread_shift), compact ? SETUP_THREADS * (pre ? LBOX_PT : LATE_PT) : SETUP_THREADS);
+                launch_pdl(c, ks, sgrid, SETUP_THREADS, st, c->idx.p, c->sv.p, xf, fp, bp, c->vis32.p, c->vis64.p, c->recs.p, c->counts.p, c->slab.p, c->ztri.p, c->tile_done.p, d_status);
                 c->launches++;
+                if (fp.lbox && b == 0 && bp.lo > 0) {        // the later batches' primitives [0, lo): boxes computed beside this k_setup
+                    prof_mark(c, st, "k_late_boxes");
+                    launch_pdl(c, k_late_boxes, div_up((size_t)bp.lo, 256 * PRE_PT), 256, st, c->idx.p, xf, fp, bp.lo, d_status);
+                    c->launches++;
+                }
             }
             if (!fp.nobin && !fp.slab_cap) {
                 const unsigned nblocks = div_up(ncnt, SCAN_THREADS * SCAN_ITEMS);
@@ -730,9 +750,9 @@ void print_timeline(const sr_ctx* c, size_t nviews) {
                 fprintf(stderr, "  [%s%d launch %.1f go %.1f end %.1f]", (k & 1) ? "tile" : "setup", k / 2, (~s.tl_launch_inv[k] - t0) * 1e-3,
                         (~s.tl_go_inv[k] - t0) * 1e-3, (s.tl_end[k] - t0) * 1e-3);
         fprintf(stderr, "\n");
-        static const char* ph[4] = {"classified", "staged", "binned", "small done"};
+        static const char* ph[7] = {"classified", "staged", "binned", "small done", "phase 1 done (compacting)", "phase 1: loads arrived", "phase 1: tests done"};
         for (int b = 0; b < 2; ++b)
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < 7; ++k)
                 if (s.ph_cnt[b][k])
                     fprintf(stderr, "  k_setup %s batch, warp reaches '%s': mean %.1f us, max %.1f us (%u warps)\n", b ? "later" : "first", ph[k],
                             (double)s.ph_sum[b][k] / s.ph_cnt[b][k] * 1e-3, (double)s.ph_max[b][k] * 1e-3, s.ph_cnt[b][k]);
@@ -820,6 +840,7 @@ int sr_create(sr_ctx** out, int device) {
     sr_ctx* c = new sr_ctx();
     c->device = device;
     if (const char* e = getenv("SR_PDL")) c->use_pdl = atoi(e) != 0;
+    if (const char* e = getenv("SR_DEBUG_SYNC")) c->debug_sync = atoi(e) != 0;
     {
         int pct = 57;                     // 146 KB of 256: five 24.5-KB k_setup CTAs (+1 KB each) fit
         if (const char* e = getenv("SR_CARVEOUT")) pct = atoi(e);
@@ -832,6 +853,7 @@ int sr_create(sr_ctx** out, int device) {
     if (const char* e = getenv("SR_ZPASS")) { c->force_zpass = atoi(e); c->depth_two_pass = c->force_zpass > 0; }
     if (const char* e = getenv("SR_ZFRAC")) c->zfrac = std::min(0.9, std::max(0.005, atof(e)));
     if (const char* e = getenv("SR_COMPACT")) c->use_compact = atoi(e) != 0;
+    if (const char* e = getenv("SR_LBOX")) c->use_lbox = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB")) c->slab_mode = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB_CAP")) c->slab_cap = std::max(1, atoi(e));
     if (const char* e = getenv("SR_NOBIN")) c->allow_nobin = atoi(e) != 0;
@@ -867,7 +889,7 @@ void sr_destroy(sr_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     c->pos.release(); c->col.release(); c->idx.release(); c->sv.release(); c->recs.release(); c->slab.release(); c->ztri.release();
-    c->tile_zmax.release();
+    c->tile_zmax.release(); c->lbox.release();
     c->counts.release(); c->cursor.release(); c->pairs.release(); c->vis32.release(); c->vis64.release();
     c->look.release(); c->ticket.release(); c->status.release(); c->tile_done.release(); c->done_bits.release();
     for (int i = 0; i < 2; ++i) {

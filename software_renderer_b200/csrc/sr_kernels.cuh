@@ -90,8 +90,8 @@ struct ViewStatus {
     unsigned long long tl_launch_inv[2 * MAX_BATCHES], tl_go_inv[2 * MAX_BATCHES], tl_end[2 * MAX_BATCHES];
     // per-warp phase times of k_setup (ns since the warp passed the grid dependency), first and later batches:
     // [batch > 0][phase]: 0 corners loaded + classified, 1 staged, 2 binned (large triangles appended), 3 small triangles rastered
-    unsigned long long ph_sum[2][4], ph_max[2][4];
-    unsigned ph_cnt[2][4];
+    unsigned long long ph_sum[2][8], ph_max[2][8];   // [..][4..6]: compacting k_setup: phase 1 done, its loads arrived, its tests done
+    unsigned ph_cnt[2][8];
 #endif
 };
 #ifdef SR_TIMELINE
@@ -99,7 +99,11 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 #define TL_BEGIN(st, slot) do { if (threadIdx.x == 0) atomicMax(&(st)->tl_launch_inv[slot], ~gtime()); } while (0)
 #define TL_GO(st, slot)    do { if (threadIdx.x == 0) atomicMax(&(st)->tl_go_inv[slot], ~gtime()); } while (0)
 #define TL_END(st, slot)   do { if ((threadIdx.x & 31) == 0) atomicMax(&(st)->tl_end[slot], gtime()); } while (0)   /* every warp: thread 0 may finish long before its CTA */
+#if SR_TIMELINE + 0 >= 2      /* per-warp phase times: three same-address atomics per warp and phase - they distort a kernel of 27 k warps */
 #define TL_PHASE(st, b, k, t0) do { if ((threadIdx.x & 31) == 0) { const unsigned long long d__ = gtime() - (t0); atomicAdd(&(st)->ph_sum[b][k], d__); atomicMax(&(st)->ph_max[b][k], d__); atomicAdd(&(st)->ph_cnt[b][k], 1u); } } while (0)
+#else
+#define TL_PHASE(st, b, k, t0) do {} while (0)
+#endif
 #else
 #define TL_BEGIN(st, slot) do {} while (0)
 #define TL_GO(st, slot)    do {} while (0)
@@ -200,11 +204,42 @@ struct FrameParams {
     int wpr;                  //   frames (set by k_tile when it retires a tile, cleared by the final batch's k_tile)
     unsigned* tile_zmax;      // two-pass depth frames: per tile, depth_ord of the farthest pixel after the front pass
                               //   (0xffffffff while a pixel of the tile is still empty)
+    unsigned* lbox;           // batched frames: one word per primitive of the later batches = its clipped bounding box in tile
+                              //   coordinates (tx0 | tx1 << 8 | ty0 << 16 | ty1 << 24; LBOX_NONE: nothing on screen), written by
+                              //   k_late_boxes; nullptr = not used
 };
+// Late bounding boxes.  In the later batches of a batched frame most triangles find every tile of their bounding box
+// retired, but finding that out costs the whole front of the setup: three index loads, nine position loads, three
+// transforms with six IEEE divisions.  None of that depends on which tiles are retired.  So a separate kernel,
+// k_late_boxes, computes the tile box of every later-batch triangle into lbox[] at full occupancy (37 registers, no
+// shared memory, two triangles per thread), and the late k_setup starts from one coalesced word per triangle: everything
+// phase 1 needs arrives in one round trip, the bitmap test is branch-free on a shared copy of the bitmap, and only the
+// survivors (~5 % on the 1M soup) run the full setup, dealt round-robin to all warps of the CTA.  16.5 + 17.5 us against
+// the 39 us of the late k_setup that transforms every triangle itself.
+// Tile coordinates must fit a byte (at most 255 tiles per axis: 4080 pixels); larger frames keep the old path.
+constexpr unsigned LBOX_NONE = 0xFFFFFFFEu;   // byte 1 (last tile column) = 0xFF cannot occur in a box
+constexpr int LBOX_MAX_TILES = 255;
+#ifndef SR_PRE_PT
+#define SR_PRE_PT 2
+#endif       // triangles per thread in the box pre-pass
+#ifndef SR_LBOX_PT
+#define SR_LBOX_PT 8
+#endif       // box words per thread in phase 1 of the late k_setup
+constexpr int PRE_PT = SR_PRE_PT, LBOX_PT = SR_LBOX_PT;
 
 // Retired-tile bitmap (batched frames).  It is constant while k_setup runs, so the loads may take the read-only path.
 __device__ __forceinline__ bool tile_retired(const FrameParams& fp, int tx, int ty) {
     return (__ldg(&fp.done_bits[ty * fp.wpr + (tx >> 5)]) >> (tx & 31)) & 1u;
+}
+// the same test on a copy of the bitmap in shared memory (late k_setup with box words: eight tests per thread)
+__device__ __forceinline__ bool row_has_open_in(const unsigned* bits, int wpr, int ty, int txa, int txb) {
+    const unsigned* row = bits + ty * wpr;
+    const int wa = txa >> 5, wb = txb >> 5;
+    const unsigned first = 0xffffffffu << (txa & 31), last = 0xffffffffu >> (31 - (txb & 31));
+    if (wa == wb) return (~row[wa] & first & last) != 0u;
+    if (~row[wa] & first) return true;
+    for (int w = wa + 1; w < wb; ++w) if (~row[w]) return true;
+    return (~row[wb] & last) != 0u;
 }
 // any tile of row `ty`, columns [txa, txb], still open?
 __device__ __forceinline__ bool row_has_open(const FrameParams& fp, int ty, int txa, int txb) {
@@ -290,7 +325,72 @@ struct XformIn {
 // LATE_PT triangles per thread and pushes the survivors' indices on a CTA-wide list; phase 2 runs the full setup on
 // the list with dense warps.  Without it every warp that holds ONE survivor walks the whole binning path with 31 idle
 // lanes (48 % of the warps at a 2 % survival rate).  Results are identical: visibility is max(index), list order free.
-template <bool DEPTH, bool BIN, bool XFORM, bool COMPACT = false>
+// Clipped bounding box, in tiles, of a triangle with screen corners a, b, c: exactly the tiles the full setup below derives
+// (truncation is monotone, so the sorted corners' rows s0.y / s2.y of R:271 are the min / max of the truncated rows: the box
+// needs no sort).  Returns the lbox word; `skip` = a corner outside the valid domain (the reference traps, R:251, R:271).
+__device__ __forceinline__ unsigned tile_box_word(const FrameParams& fp, float ax, float ay, float bx, float by, float cx, float cy, bool& skip) {
+    skip = !(in_domain(ax) && in_domain(ay) && in_domain(bx) && in_domain(by) && in_domain(cx) && in_domain(cy));
+    if (skip) return LBOX_NONE;
+    const int px0 = __float2int_rz(ax), px1 = __float2int_rz(bx), px2 = __float2int_rz(cx);
+    const int qy0 = __float2int_rz(ay), qy1 = __float2int_rz(by), qy2 = __float2int_rz(cy);       // frame rows
+    const int ya = max(min(qy0, min(qy1, qy2)) - fp.y_org, 0), yb = min(max(qy0, max(qy1, qy2)) - fp.y_org, fp.height - 1);
+    const int xa = max(min(px0, min(px1, px2)), 0), xb = min(max(px0, max(px1, px2)), fp.width - 1);
+    if (ya > yb || xa > xb) return LBOX_NONE;
+    return (unsigned)(xa >> TILE_SHIFT) | ((unsigned)(xb >> TILE_SHIFT) << 8) | ((unsigned)(ya >> TILE_SHIFT) << 16) | ((unsigned)(yb >> TILE_SHIFT) << 24);
+}
+
+// Box pre-pass of a batched frame: lbox[p] for the primitives [0, n) of the later batches.  PRE_PT triangles per thread,
+// loads issued together (indices, then positions), the same transform and the same box arithmetic as the full setup.
+// A triangle outside the valid domain is counted HERE, once per frame, and never reaches a later batch.
+// Ordering (programmatic dependent launch): the kernel follows the first batch's k_setup in the stream.  It lets its
+// own dependents be scheduled at once, works WITHOUT waiting for k_setup (it reads only the mesh and the matrix, and
+// lbox[] has no reader left: this frame's k_setup CTAs have all passed their own wait, so the previous frame's kernels
+// are complete), and waits at its END, so that "k_late_boxes complete" still implies "k_setup complete" for k_tile.
+// Its CTAs therefore move in as k_setup's single wave thins out: 150.0 us per frame against 154.2 with the wait at the
+// start (1M soup).  (The same work as extra CTAs inside k_setup's own grid faulted, non-deterministically, in a way that
+// followed ptxas' register allocation of the fused kernel and no memory access of the source: DESIGN.md §8.)
+__global__ void __launch_bounds__(256) k_late_boxes(const int* __restrict__ idx, XformIn xf, FrameParams fp, int n,
+                                                    ViewStatus* __restrict__ status) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    TL_BEGIN(status, 2 * MAX_BATCHES - 2);               // timeline build: the pre-pass shows as "setup7"
+    TL_GO(status, 2 * MAX_BATCHES - 2);
+    int pid[PRE_PT], ii[PRE_PT][3];
+#pragma unroll
+    for (int k = 0; k < PRE_PT; ++k) {
+        pid[k] = ((int)blockIdx.x * PRE_PT + k) * 256 + (int)threadIdx.x;
+        const bool in = pid[k] < n;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) ii[k][q] = in ? __ldg(&idx[3 * (size_t)pid[k] + q]) : 0;
+    }
+    float ps[PRE_PT][3][3];
+#pragma unroll
+    for (int k = 0; k < PRE_PT; ++k)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            ps[k][q][0] = __ldg(&xf.pos[3 * (size_t)ii[k][q]]); ps[k][q][1] = __ldg(&xf.pos[3 * (size_t)ii[k][q] + 1]); ps[k][q][2] = __ldg(&xf.pos[3 * (size_t)ii[k][q] + 2]);
+        }
+    unsigned nskip = 0;
+#pragma unroll
+    for (int k = 0; k < PRE_PT; ++k) {
+        float sx[3], sy[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const float3 t = transform_to_screen<false>(xf.M, ps[k][q][0], ps[k][q][1], ps[k][q][2], xf.fw, xf.fh);
+            sx[q] = t.x; sy[q] = t.y;
+        }
+        bool skip = false;
+        const unsigned word = tile_box_word(fp, sx[0], sy[0], sx[1], sy[1], sx[2], sy[2], skip);
+        if (pid[k] < n) fp.lbox[pid[k]] = word;
+        nskip += __popc(__ballot_sync(0xffffffffu, skip && pid[k] < n));
+    }
+    if ((threadIdx.x & 31) == 0 && nskip) atomicAdd(&status->domain_skipped, nskip);
+    TL_END(status, 2 * MAX_BATCHES - 2);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+// PRE = true (later batches of a batched frame with fp.lbox; always with COMPACT): phase 1's answer comes from lbox[]
+// (see "Late bounding boxes" above).
+template <bool DEPTH, bool BIN, bool XFORM, bool COMPACT = false, bool PRE = false>
 __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH ? SR_SETUP_DEPTH_MINB : (BIN ? SR_SETUP_MINB : 2048 / SETUP_THREADS))) k_setup(const int* __restrict__ idx, float4* __restrict__ sv, XformIn xf, FrameParams fp,
                                                BatchParams bp, unsigned* __restrict__ vis32,
                                                unsigned long long* __restrict__ vis64, TriRec* __restrict__ recs,
@@ -308,11 +408,25 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
     __shared__ BaryT s_bt[DEPTH ? SETUP_THREADS : 1];
     __shared__ float s_z[DEPTH ? SETUP_THREADS : 1][3];
     __shared__ unsigned s_tally;                            // (warps finished) << 16 | small triangles of the CTA
-    __shared__ int s_list[COMPACT ? SETUP_THREADS * LATE_PT : 1];   // COMPACT: primitives that survived phase 1
+    __shared__ int s_list[COMPACT ? SETUP_THREADS * (PRE ? LBOX_PT : LATE_PT) : 1];   // COMPACT: primitives that survived phase 1
     __shared__ int s_nsurv;
 
     const bool late = fp.batched && bp.index > 0;                   // only later batches can meet retired tiles
-    if (late && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
+    // COMPACT && PRE: everything phase 1 needs is requested in ONE round trip - the retired count, the thread's LBOX_PT
+    // box words and the CTA's copy of the retired-tile bitmap (at most 8 x 255 words) - before anything is waited for
+    constexpr int LBOX_BITS = (COMPACT && PRE) ? 8 * LBOX_MAX_TILES : 1;
+    __shared__ unsigned s_bits[LBOX_BITS];
+    unsigned w[(COMPACT && PRE) ? LBOX_PT : 1];
+    if (COMPACT && PRE) {
+        const unsigned retired = late ? *(volatile const unsigned*)&status->tiles_done : 0u;
+#pragma unroll
+        for (int k = 0; k < LBOX_PT; ++k) {
+            const int p = bp.lo + (blockIdx.x * LBOX_PT + k) * SETUP_THREADS + (int)threadIdx.x;
+            w[k] = p < bp.hi ? __ldg(&fp.lbox[p]) : LBOX_NONE;
+        }
+        for (int q = threadIdx.x; q < fp.wpr * fp.tiles_y; q += SETUP_THREADS) s_bits[q] = __ldg(&fp.done_bits[q]);
+        if (retired >= (unsigned)fp.ntiles) return;                  // every tile already retired
+    } else if (late && status->tiles_done >= (unsigned)fp.ntiles) return;     // every tile already retired
     if (fp.batched && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&status->batches_run, 1u);
     if (threadIdx.x == 0) { s_tally = 0; s_nsurv = 0; }
     __syncthreads();                                         // all warps arrive together
@@ -320,7 +434,63 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
     const unsigned lane = threadIdx.x & 31;
     const int wbase = threadIdx.x & ~31;
     int nsurv = 1;                                           // !COMPACT: the loop below runs once, one triangle per thread
-    if (COMPACT) {
+    if (COMPACT && PRE) {
+        // Phase 1 from the pre-pass: LBOX_PT box words per thread (coalesced, all in flight at once), then the retired-tile
+        // bitmap; the survivors' indices go on the CTA-wide list (order is free: visibility is max(index)).
+        // (the words and the bitmap copy were requested at the top of the kernel; the barrier there published s_bits)
+        TL_PHASE(status, tl_b, 5, tl_t0);
+        unsigned survbits = 0u;
+#pragma unroll
+        for (int k = 0; k < LBOX_PT; ++k) {
+            bool surv = false;
+            if ((w[k] & 0xff00u) != 0xff00u) {
+                const int ta = w[k] & 255, tb = (w[k] >> 8) & 255, ra = (w[k] >> 16) & 255, rb = w[k] >> 24;
+                // up to eight tile rows, tested without a branch: eight independent shared loads of the word that holds the
+                // box's first column (a divergent row-by-row loop with dependent loads cost 2000 cycles per word here, 9 of
+                // the kernel's 23 us); a box that crosses a 32-tile word boundary adds its last word, wider ones the loop
+                surv = rb - ra >= 8;                        // tall footprints are tested row by row in phase 2
+                if (!surv) {
+                    const int wa = ta >> 5, wb = tb >> 5;
+                    const unsigned first = 0xffffffffu << (ta & 31), last = 0xffffffffu >> (31 - (tb & 31));
+                    const unsigned ma = wa == wb ? (first & last) : first;
+                    unsigned open = 0u;
+#pragma unroll
+                    for (int d = 0; d < 8; ++d) open |= ~s_bits[min(ra + d, rb) * fp.wpr + wa] & ma;      // rows past rb repeat rb
+                    if (wb != wa) {
+#pragma unroll
+                        for (int d = 0; d < 8; ++d) open |= ~s_bits[min(ra + d, rb) * fp.wpr + wb] & last;
+                        if (wb - wa > 1)
+                            for (int ty = ra; ty <= rb && !open; ++ty) open = row_has_open_in(s_bits, fp.wpr, ty, ta, tb) ? 1u : 0u;
+                    }
+                    surv = open != 0u;
+                }
+            }
+            survbits |= surv ? (1u << k) : 0u;
+        }
+        // one list reservation per warp for all LBOX_PT words (order inside the list is free)
+        unsigned m_surv[LBOX_PT];
+        int mine = 0, total = 0;                             // survivors of lower lanes and lower words; of the warp
+#pragma unroll
+        for (int k = 0; k < LBOX_PT; ++k) {
+            m_surv[k] = __ballot_sync(0xffffffffu, (survbits >> k) & 1u);
+            total += __popc(m_surv[k]);
+        }
+        if (total) {                                         // warp-uniform
+            int at = 0;
+            if (lane == 0) at = atomicAdd(&s_nsurv, total);
+            at = __shfl_sync(0xffffffffu, at, 0);
+#pragma unroll
+            for (int k = 0; k < LBOX_PT; ++k) {
+                if ((survbits >> k) & 1u)
+                    s_list[at + mine + __popc(m_surv[k] & ((1u << lane) - 1u))] = bp.lo + (blockIdx.x * LBOX_PT + k) * SETUP_THREADS + (int)threadIdx.x;
+                mine += __popc(m_surv[k]);
+            }
+        }
+        TL_PHASE(status, tl_b, 6, tl_t0);
+        __syncthreads();
+        nsurv = s_nsurv;
+        TL_PHASE(status, tl_b, 4, tl_t0);
+    } else if (COMPACT) {
         // Phase 1.  The loads of the thread's LATE_PT triangles are issued together (indices, then corners): the phase is
         // two dependent memory round trips, so its throughput is the number of loads in flight.
         __shared__ unsigned s_hist[DEPTH ? ZHIST_BINS : 1];
@@ -419,11 +589,15 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
     }
     unsigned small_tally = 0;
     for (int lbase = 0; lbase < nsurv; lbase += SETUP_THREADS) {
-    if (COMPACT && lbase + wbase >= nsurv) break;            // warp-uniform: this warp has no survivor left
+    // COMPACT: the survivors are dealt round-robin to the CTA's warps (spot = lane * warps + warp), so a short list is
+    // shared by all warps instead of filling the first ones: every warp's chain of dependent work (loads, binning
+    // rounds, appends) is 1/8 as long
+    const int spot = lbase + (int)lane * (SETUP_THREADS / 32) + (int)(threadIdx.x >> 5);
+    if (COMPACT && lbase + (int)(threadIdx.x >> 5) >= nsurv) break;            // warp-uniform: this warp has no survivor left
     const int gtid = (int)(blockIdx.x * blockDim.x + threadIdx.x);
     const bool holds = (threadIdx.x & ((1u << bp.spread_shift) - 1u)) == 0u;          // spread: every 2^shift-th lane holds a triangle
-    const bool valid = COMPACT ? (lbase + (int)threadIdx.x < nsurv) : (holds && bp.lo + (gtid >> bp.spread_shift) < bp.hi);
-    const int prim = COMPACT ? (valid ? s_list[lbase + threadIdx.x] : 0) : bp.lo + (gtid >> bp.spread_shift);
+    const bool valid = COMPACT ? (spot < nsurv) : (holds && bp.lo + (gtid >> bp.spread_shift) < bp.hi);
+    const int prim = COMPACT ? (valid ? s_list[spot] : 0) : bp.lo + (gtid >> bp.spread_shift);
     bool skipped = false, tiny = false, small = false, large = false;
     SortedTri s = {};
     int ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, y0 = 0, y1 = -1, xmin = 0, xmax = -1;
@@ -622,6 +796,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
             }
         });
         if (seg_max) atomicMax(&status->seg_max, seg_max);          // a segment overflowed: the host grows the slabs and re-runs
+
     }
 
     TL_PHASE(status, tl_b, 2, tl_t0);

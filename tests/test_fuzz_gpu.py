@@ -20,6 +20,7 @@ POLICIES = [
     {"SR_SLAB_CAP": "2"},
     {"SR_BATCHES": "3"},
     {"SR_BATCHES": "3", "SR_SLAB": "0"},
+    {"SR_BATCHES": "3", "SR_LBOX": "0"},        # batched frames without the box pre-pass (what frames wider than 4080 pixels get)
     {"SR_NOBIN": "0"},
     {"SR_PDL": "0"},
 ]
