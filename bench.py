@@ -288,7 +288,10 @@ def roofline_of(acc, ntris, nverts, W, H, workload_key):
     vertex of xyz + rgb, 8 B per pixel of colour + depth) are split over the kernels that touch them:
     positions are read by k_transform, or - in batched frames, which do not launch it - by k_setup."""
     hbm, peak_kind = peaks()
+    # (with the box pre-pass of batched frames the later batches' indices and positions are read by k_late_boxes; charged in
+    # full to either kernel, an upper bound for each: the split depends on the batch sizes)
     alg = {"k_transform": 12 * nverts, "k_setup": 12 * ntris + (0 if "k_transform" in acc else 12 * nverts),
+           "k_late_boxes": 12 * ntris + 12 * nverts,
            "k_tile": 12 * nverts + 8 * W * H, "k_resolve": 12 * nverts + 8 * W * H}
     top = max(acc, key=acc.get) if acc else "k_tile"
     top_ms = acc.get(top, float("nan"))

@@ -202,6 +202,7 @@ struct sr_ctx {
     // adaptive policy (depth off): index-descending batches pay off when most tile-list entries are never read
     bool batched_mode = false;
     unsigned long long single_batch_pairs = 0;
+    std::vector<double> schedule;        // SR_SCHEDULE: forced batch shares (experiments); empty = two batches sized by first_frac
     double first_frac = 0.125;           // batched frames: share of the primitives (from the top) in the first batch
     int force_batches = -1;              // SR_BATCHES env: 0 = never, 1 = always, -1 = adaptive
     bool use_pdl = true;
@@ -498,9 +499,21 @@ int enqueue_view(sr_ctx* c, const float* transform, int prim, int W, int H, int 
         if (fp.batched) {
             // two index-descending batches: the top `first_frac` of the primitives (sized from how much of the tile
             // lists a single-batch frame consumed), then the rest, which mostly finds its tiles retired
-            const int first = std::min(ntris - 1, std::max(1, (int)((double)ntris * c->first_frac)));
-            batches[nb++] = BatchParams{ntris - first, ntris, 0, 0, 0};
-            batches[nb++] = BatchParams{0, ntris - first, 0, 1, 1};
+            if (c->schedule.empty()) {
+                const int first = std::min(ntris - 1, std::max(1, (int)((double)ntris * c->first_frac)));
+                batches[nb++] = BatchParams{ntris - first, ntris, 0, 0, 0};
+                batches[nb++] = BatchParams{0, ntris - first, 0, 1, 1};
+            } else {
+                // SR_SCHEDULE=f0,f1,...: shares of the primitives, from the top, of the first batches; the last batch takes the rest
+                int hi = ntris;
+                for (size_t q = 0; q < c->schedule.size() && nb < MAX_BATCHES - 1 && hi > 1; ++q) {
+                    const int n = std::min(hi - 1, std::max(1, (int)((double)ntris * c->schedule[q])));
+                    batches[nb] = BatchParams{hi - n, hi, 0, nb, 0};
+                    hi -= n; nb++;
+                }
+                batches[nb] = BatchParams{0, hi, 0, nb, 1};
+                nb++;
+            }
         } else if (two_pass) {
             if (!c->zsplit_valid) { c->zsplit = c->zh_lo + 0.25f * (c->zh_hi - c->zh_lo); c->zsplit_valid = true; }
             const float scale = c->zh_hi > c->zh_lo ? (float)ZHIST_BINS / (c->zh_hi - c->zh_lo) : 0.0f;
@@ -854,6 +867,9 @@ int sr_create(sr_ctx** out, int device) {
     if (const char* e = getenv("SR_ZFRAC")) c->zfrac = std::min(0.9, std::max(0.005, atof(e)));
     if (const char* e = getenv("SR_COMPACT")) c->use_compact = atoi(e) != 0;
     if (const char* e = getenv("SR_LBOX")) c->use_lbox = atoi(e) != 0;
+    if (const char* e = getenv("SR_SCHEDULE")) {
+        for (const char* q = e; *q;) { char* end = nullptr; const double f = strtod(q, &end); if (end == q) break; if (f > 0.0 && f < 1.0) c->schedule.push_back(f); q = *end ? end + 1 : end; }
+    }
     if (const char* e = getenv("SR_SLAB")) c->slab_mode = atoi(e) != 0;
     if (const char* e = getenv("SR_SLAB_CAP")) c->slab_cap = std::max(1, atoi(e));
     if (const char* e = getenv("SR_NOBIN")) c->allow_nobin = atoi(e) != 0;

@@ -669,7 +669,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
         }
     }
     int tx0 = xmin >> TILE_SHIFT, tx1 = xmax >> TILE_SHIFT, ty0 = y0 >> TILE_SHIFT, ty1 = y1 >> TILE_SHIFT;
-    if (late && (small || large)) {
+    if (late && (small || large) && !(COMPACT && PRE)) {      // (COMPACT && PRE: phase 1 made this very test, on the same box)
         // retire triangles whose bbox tiles are all done: a few words of the retired-tile bitmap per tile row (taller
         // footprints are tested row by row where their tile-row items are processed)
         if (ty1 - ty0 < 8) {
@@ -763,7 +763,8 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
         warp_balance(large ? (ty1 - ty0 + 1) : 0, [&](int src, int item) {
             const StagedRect r = s_rect[wbase + src];
             const int cs = r.w >> 16, ty = r.ty0 + item;
-            if (late && !row_has_open(fp, ty, r.tx0, r.tx0 + (r.w & 0x7fff) - 1)) return;
+            if (late && !((COMPACT && PRE) ? row_has_open_in(s_bits, fp.wpr, ty, r.tx0, r.tx0 + (r.w & 0x7fff) - 1)
+                                           : row_has_open(fp, ty, r.tx0, r.tx0 + (r.w & 0x7fff) - 1))) return;
             int ta, tb;
             tile_row_range(src, r, ty, ta, tb);
             const unsigned seg0 = (unsigned)(ty * fp.tiles_x) * NCHUNK + cs;
@@ -777,7 +778,7 @@ __global__ void __launch_bounds__(SETUP_THREADS, COMPACT ? SR_LATE_MINB : (DEPTH
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     pos[u] = 0xffffffffu;
-                    if (tx + u <= tb && !(late && tile_retired(fp, tx + u, ty))) {
+                    if (tx + u <= tb && !(late && ((COMPACT && PRE) ? ((s_bits[ty * fp.wpr + ((tx + u) >> 5)] >> ((tx + u) & 31)) & 1u) != 0u : tile_retired(fp, tx + u, ty)))) {
                         pos[u] = atomicAdd(&counts[seg0 + (tx + u) * NCHUNK], 1u);
                         if (DEPTH && bp.zpass == 2) tile_done[ty * fp.tiles_x + tx + u] = fp.epoch;
                     }
