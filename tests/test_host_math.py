@@ -178,3 +178,33 @@ def test_float32_quotient_with_one_remainder_step_is_exact():
         a = np.clip(k * d + delta, 0, (1 << 22) - 1)
         check(a, d)
     check(np.full(4096, (1 << 22) - 1), np.arange(1, 4097))                     # largest numerator
+
+
+def test_late_box_word_equals_the_full_setups_tile_range():
+    """csrc/sr_kernels.cuh::tile_box_word (k_late_boxes) restated with numpy: the clipped tile box taken from the min / max of
+    the TRUNCATED corners equals the one the full setup derives after its stable 3-sort on the float rows (truncation toward
+    zero is monotone, so the sorted corners' rows are the min / max of the truncated rows); the word's second byte is 0xFF
+    only for 'nothing on screen'; bands (y_org) shift rows before clipping."""
+    rng = np.random.default_rng(0xB0C5)
+    for W, H, y_org in [(1920, 1080, 0), (4080, 4080, 0), (333, 251, 0), (1920, 135, 405), (17, 9, 3)]:
+        n = 20000
+        scale = rng.choice([0.3, 1.0, 3.0, 50.0], size=(n, 1, 1))
+        c = rng.uniform(-0.4, 1.4, size=(n, 1, 2)) * np.array([W, H + y_org])
+        xy = (c + rng.normal(size=(n, 3, 2)) * scale * 40.0).astype(np.float32)
+        xy[rng.random(n) < 0.05] *= np.float32(-1.0)                       # negative coordinates: truncation goes UP
+        ix = np.trunc(xy[..., 0]).astype(np.int64)
+        iy = np.trunc(xy[..., 1]).astype(np.int64)
+        # the box pre-pass: min / max of the truncated corners, rows moved to the band, clipped
+        ya = np.maximum(iy.min(1) - y_org, 0); yb = np.minimum(iy.max(1) - y_org, H - 1)
+        xa = np.maximum(ix.min(1), 0); xb = np.minimum(ix.max(1), W - 1)
+        on = (ya <= yb) & (xa <= xb)
+        word = (xa >> 4) | ((xb >> 4) << 8) | ((ya >> 4) << 16) | ((yb >> 4) << 24)
+        word = np.where(on, word, 0xFFFFFFFE)
+        # the full setup: stable insertion sort with strict < on the FLOAT rows, then truncate and clip (R:271-273)
+        order = np.argsort(xy[..., 1], axis=1, kind="stable")
+        sy = np.take_along_axis(iy, order, 1) - y_org
+        y0 = np.maximum(sy[:, 0], 0); y1 = np.minimum(sy[:, 2], H - 1)
+        assert np.array_equal(on, (y0 <= y1) & (xa <= xb))
+        full = (xa >> 4) | ((xb >> 4) << 8) | ((y0 >> 4) << 16) | ((y1 >> 4) << 24)
+        assert np.array_equal(word[on], full[on])
+        assert not (((word[on] >> 8) & 0xFF) == 0xFF).any() and (((word[~on] >> 8) & 0xFF) == 0xFF).all()

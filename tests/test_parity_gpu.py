@@ -311,6 +311,32 @@ def test_batched_mode_is_identical(batched_renderer, case):
         assert_same(r, v, i, S.app_transform(0.7), 1024, 1024)
 
 
+@pytest.mark.parametrize("W", [4080, 4096])
+def test_batched_wide_frames_at_the_box_word_limit(batched_renderer, W):
+    """A box word of the late-batch pre-pass (k_late_boxes) holds tile coordinates up to 254: a frame of 255 tile columns
+    (4080 pixels) still takes it, one of 256 the path that transforms every late triangle itself.  Both are the oracle's image."""
+    v, i = random_tris(71, 70_000, spread=1.1, small=0.02)
+    assert_same(batched_renderer, v, i, I4, W, 48)
+    assert batched_renderer.stats()["batches_run"] >= 1
+
+
+@pytest.mark.parametrize("case", ["sparse", "all_retired"])
+def test_batched_domain_skips_of_the_later_batch_are_counted(batched_renderer, case):
+    """Triangles outside the valid domain (the reference traps, R:251 / R:271) among the LOW indices, i.e. in the later batch of
+    a batched frame: skipped, counted once each, the call reports the domain error - also when the first batch retires
+    every tile and the later batch's own kernels leave at once (the count then comes from the box pre-pass)."""
+    if case == "sparse":
+        v, i = random_tris(72, 70_000, spread=0.4, small=0.01)
+    else:
+        v, i = random_tris(73, 70_000, spread=1.2, small=0.3)
+    v = v.copy()
+    for t in (5, 6, 7):
+        v[3 * t + 1, 0] = np.inf                      # one corner of triangles 5, 6, 7 has no finite screen position
+    assert_same(batched_renderer, v, i, I4, 640, 480, expect_domain=True)
+    assert batched_renderer.stats()["domain_skipped"] == 3
+    assert batched_renderer.stats()["batches_run"] == (2 if case == "sparse" else 1)
+
+
 def test_adaptive_policy_switches_and_stays_exact(renderer):
     v, i = S.triangle_soup(300_000, 1280, 720, seed=12)
     seen = set()
