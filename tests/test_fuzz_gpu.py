@@ -22,6 +22,8 @@ POLICIES = [
     {"SR_BATCHES": "3", "SR_SLAB": "0"},
     {"SR_BATCHES": "3", "SR_LBOX": "0"},        # batched frames without the box pre-pass (what frames wider than 4080 pixels get)
     {"SR_NOBIN": "0"},
+    {"SR_ZPASS": "1"},                                             # experiment knobs that stay in the tree: two-pass depth frames,
+    {"SR_BATCHES": "3", "SR_LBOX": "0", "SR_COMPACT": "1"},        # ... the compacting late k_setup without box words
     {"SR_PDL": "0"},
 ]
 
