@@ -32,6 +32,6 @@ print(f"# Static SASS opcode counts per kernel — `{os.path.relpath(lib, ROOT)}
 print("| kernel | total | " + " | ".join(g for g, _ in groups) + " |")
 print("|---|---:|" + "---:|" * len(groups))
 for k, c in ops.items():
-    if not re.match(r"k_(tile|setup|transform|resolve)", k):
+    if not re.match(r"k_(tile|setup|transform|resolve|late_boxes|points|na_)", k):
         continue
     print(f"| `{k}` | {sum(c.values())} | " + " | ".join(str(sum(n for o, n in c.items() if f(o))) for _, f in groups) + " |")
